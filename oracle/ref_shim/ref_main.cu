@@ -1,0 +1,549 @@
+// ref_main.cu — headless Linux driver for the UNMODIFIED reference render path.
+//
+// TEST / MEASUREMENT INFRASTRUCTURE ONLY. This translation unit #includes the reference's
+// own headers from /root/reference (through a symlink overlay made by oracle/Makefile) and
+// launches the reference's own kernels: CUDAKernels::initRandState, initMesh,
+// createRandomWorld, createBVH and render (reference: CudaRayTracer/src/CUDAKernels.h),
+// through the reference's own host class CUDARenderer (src/CUDARenderer.cuh).
+// Nothing here is linked into libcrt_b200.so. It exists to
+//   (1) time the reference kernel on the same B200 as the new implementation
+//       (`bench.py --impl reference`), and
+//   (2) dump reference outputs that pin the CPU oracle and the new kernels:
+//       RGBA8 image, float radiance, primary-hit primitive ids + t, ray counts,
+//       the reference builder's triangle permutation, and cuRAND XORWOW known answers.
+//
+// What replaces what (all host side; device hit/scatter/render code is byte-for-byte):
+//   - EntryPoint.cu / Raytracer.h / WindowManager.h (SFML window loop)  -> main() below
+//   - SceneManager.h (tinyobjloader + assets/, both absent upstream)     -> build_world() below,
+//     which performs the same launches in the same order (SceneManager.h:77-98,170-195)
+//     on procedurally generated arrays (scene_gen.cpp)
+//   - Core/Core.cuh (does not compile on Linux)                          -> overlay_src/Core.cuh
+//   - `const int MAX_BOUNCES = 20` (CUDAKernels.h:106) becomes the compile-time macro
+//     REF_MAX_BOUNCES (default 20) so the 8-bounce configs can be built.
+//
+// The "twin" kernels at the bottom are the shim's own code; they call the reference's
+// device functions (getRay, BVHNode::hit, Material::scatter/emit) and only add counters and
+// float outputs. Their RGBA8 output is compared bit-for-bit with the unmodified render
+// kernel's in every run that uses them (field "twin_matches_render").
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <string>
+#include <vector>
+#include <map>
+#include <array>
+#include <chrono>
+#include <iostream>
+#include <stdexcept>
+#include <limits>
+#include <cuda_runtime.h>
+#include <device_launch_parameters.h>
+#include <curand_kernel.h>
+
+#ifndef REF_MAX_BOUNCES
+#define REF_MAX_BOUNCES 20
+#endif
+
+// The shim needs to set the camera's yaw/pitch (no window to fly it) and to read the mesh
+// arrays back for the primitive-id dump. Standard headers are all included above.
+#define private public
+#define protected public
+#include "CUDAHelpers.h"
+#include "CUDAKernels.h"
+#include "CUDARenderer.cuh"
+#undef private
+#undef protected
+
+#include "scene_gen.h"
+
+#define CK(x) CUDA_CHECK(x)
+
+// ---------------------------------------------------------------------------------------
+// shim kernels
+// ---------------------------------------------------------------------------------------
+
+// Scene injection for scenes whose sphere list is not the two hard-coded spheres of
+// createRandomWorld (CUDAKernels.h:56-84). Same construction order: materials, meshes, spheres.
+__global__ void shimCreateWorld(CRT::HittableList* world, CRT::Mesh* meshes, int numMeshes,
+                                CRT::MaterialData* materialsData, int materialsNum,
+                                const float* spheres, const int* sphereMat, int numSpheres, int* objectsNum) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        new (world) CRT::HittableList();
+        CUDAKernels::createMaterialsKernel(world, materialsData, materialsNum);
+        for (int i = 0; i < numMeshes; ++i) world->add(&meshes[i]);
+        for (int i = 0; i < numSpheres; ++i)
+            world->add(new CRT::Sphere(CRT::Vec3(spheres[4 * i], spheres[4 * i + 1], spheres[4 * i + 2]),
+                                       spheres[4 * i + 3], sphereMat[i]));
+        *objectsNum = world->m_NumObjects;
+    }
+}
+
+// Twin of CUDAKernels::render + rayColor with counters and float output.
+__global__ void shimRenderTwin(unsigned char* data, float* radiance, unsigned long long* rayCount,
+                               CRT::BVHNode* root, CRT::HittableList* world, curandState* rand_state,
+                               int W, int H) {
+    int x = threadIdx.x + blockIdx.x * blockDim.x;
+    int y = threadIdx.y + blockIdx.y * blockDim.y;
+    if (x >= W || y >= H) return;
+    int pix = y * W + x;
+    curandState rng = rand_state[pix];
+    unsigned long long rays = 0;
+    CRT::Color sum(0, 0, 0);
+    for (int s = 0; s < CRT::d_camera.m_SamplesPerPixel; s++) {
+        CRT::Ray ray = CRT::d_camera.getRay(x, y, W, H, &rng);
+        CRT::Color thr(1.0f, 1.0f, 1.0f);
+        CRT::Color result(0.0f, 0.0f, 0.0f);
+        bool done = false;
+        for (int bounce = 0; bounce < REF_MAX_BOUNCES && !done; bounce++) {
+            CRT::HitInfo rec;
+            if (bounce >= 3) {
+                float p = fminf(fmaxf(thr.x(), fmaxf(thr.y(), thr.z())), 0.95f);
+                if (curand_uniform(&rng) > p) break;
+                thr /= p;
+            }
+            rays++;
+            if (root->hit(ray, CRT::Interval(0.001f, INFINITY), rec)) {
+                CRT::Ray scattered{};
+                CRT::Color att{};
+                if (rec.MaterialIndex >= 0 && rec.MaterialIndex < world->m_NumMaterials) {
+                    if (world->m_Materials[rec.MaterialIndex]->scatter(ray, rec, att, scattered, &rng)) {
+                        thr *= att;
+                        ray = scattered;
+                    } else {
+                        result = world->m_Materials[rec.MaterialIndex]->emit();
+                        done = true;
+                    }
+                }
+            } else {
+                result = thr * CRT::getBackgroundColor(ray);
+                done = true;
+            }
+        }
+        sum += result;
+    }
+    CRT::Color out = CRT::d_camera.m_PixelSampleScale * sum;
+    radiance[3 * pix + 0] = out.x();
+    radiance[3 * pix + 1] = out.y();
+    radiance[3 * pix + 2] = out.z();
+    CRT::writeColor(data, pix * 4, out);
+    rand_state[pix] = rng;
+    atomicAdd(rayCount, rays);
+}
+
+// Primary-hit dump: sample 0's camera ray from a fresh stream, the reference's own
+// traversal, then identification of the primitive by replaying the reference's own
+// intersection routines over every primitive in the reference's visiting order
+// (object order; inside a mesh the permuted index order) — the last primitive that
+// reproduces the winning t bit-for-bit is the one the reference kept (ties replace).
+__global__ void shimPrimaryDump(int* outObj, int* outTriPos, float* outT,
+                                CRT::BVHNode* root, CRT::HittableList* world, int numMeshes,
+                                unsigned long long seed, int W, int H) {
+    int x = threadIdx.x + blockIdx.x * blockDim.x;
+    int y = threadIdx.y + blockIdx.y * blockDim.y;
+    if (x >= W || y >= H) return;
+    int pix = y * W + x;
+    curandState rng;
+    curand_init(seed, pix, 0, &rng);
+    CRT::Ray ray = CRT::d_camera.getRay(x, y, W, H, &rng);
+    CRT::HitInfo rec;
+    int obj = -1, tripos = -1;
+    float t = INFINITY;
+    if (root->hit(ray, CRT::Interval(0.001f, INFINITY), rec)) {
+        t = rec.IntersectionTime;
+        for (int o = 0; o < world->m_NumObjects; o++) {
+            if (o < numMeshes) {
+                const CRT::Mesh* m = static_cast<const CRT::Mesh*>(world->m_Objects[o]);
+                for (int i = 0; i < (int)m->m_IndexCount; i += 3) {
+                    CRT::HitInfo tmp;
+                    if (m->rayTriangleIntersect(ray, m->m_Vertices[m->m_Indices[i]], m->m_Vertices[m->m_Indices[i + 1]],
+                                                m->m_Vertices[m->m_Indices[i + 2]], CRT::Interval(0.001f, INFINITY), tmp, i)) {
+                        if (tmp.IntersectionTime == t) { obj = o; tripos = i / 3; }
+                    }
+                }
+            } else {
+                CRT::HitInfo tmp;
+                if (world->m_Objects[o]->hit(ray, CRT::Interval(0.001f, INFINITY), tmp)) {
+                    if (tmp.IntersectionTime == t) { obj = o; tripos = 0; }
+                }
+            }
+        }
+    }
+    outObj[pix] = obj;
+    outTriPos[pix] = tripos;
+    outT[pix] = t;
+}
+
+// cuRAND XORWOW known answers: n outputs of curand() and curand_uniform() bits per (seed, subseq).
+__global__ void shimRngKat(const unsigned long long* seeds, const unsigned long long* subseqs, int cases, int n,
+                           unsigned int* outState, unsigned int* outRaw, float* outUniform) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cases) return;
+    curandState st;
+    curand_init(seeds[c], subseqs[c], 0, &st);
+    for (int k = 0; k < 5; k++) outState[c * 6 + k] = st.v[k];
+    outState[c * 6 + 5] = st.d;
+    curandState a = st, b = st;
+    for (int i = 0; i < n; i++) {
+        outRaw[c * n + i] = curand(&a);
+        outUniform[c * n + i] = curand_uniform(&b);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// host
+// ---------------------------------------------------------------------------------------
+struct Args {
+    std::string scene = "cornell";
+    int param = 0;
+    int width = 256, height = 256;
+    int spp = 16;
+    int frames = 1, warmup = 0;
+    unsigned long long seed = 1804289383ull;   // glibc rand() first value (CUDARenderer.cuh:46)
+    std::string dump;                            // prefix for binary dumps ("" = none)
+    bool twin = false;                           // run the counting twin (untimed)
+    bool primary = false;                        // dump primary ids
+    bool rngkat = false;
+    int stack = 8192;
+    double build_timeout_s = 1800.0;
+    // camera overrides (NaN = scene default)
+    float cam[3] = {NAN, NAN, NAN};
+    float yaw = NAN, pitch = NAN, vfov = NAN, aperture = NAN, focus = NAN, aspect = NAN;
+};
+
+static void write_bin(const std::string& path, const void* p, size_t bytes) {
+    FILE* f = fopen(path.c_str(), "wb");
+    if (!f) throw std::runtime_error("cannot write " + path);
+    fwrite(p, 1, bytes, f);
+    fclose(f);
+}
+
+struct World {
+    CRT::HittableList* dWorld = nullptr;
+    CRT::BVHNode* dNodes = nullptr;
+    CRT::Mesh* dMeshes = nullptr;
+    Vertex* dVertices = nullptr;
+    uint32_t* dIndices = nullptr;
+    int* dFaceMat = nullptr;
+    CRT::MaterialData* dMats = nullptr;
+    int numMeshes = 0;
+    int numObjects = 0;
+    double mesh_build_ms = 0, world_ms = 0, top_bvh_ms = 0;
+    std::vector<uint32_t> meshIndexOffset, meshIndexCount, meshVertexOffset;
+};
+
+// Same launch sequence as SceneManager::initializeScene/initMeshes (SceneManager.h:77-98,100-196).
+static void build_world(const crt::SceneData& s, const std::string& sceneName, curandState* dRand, World& w) {
+    using clk = std::chrono::steady_clock;
+    CK(cudaMalloc(&w.dWorld, sizeof(CRT::HittableList)));
+    int* dObjectsNum = nullptr;
+    CK(cudaMallocManaged(&dObjectsNum, sizeof(int)));
+
+    w.numMeshes = (int)s.num_meshes();
+    // Vertex AoS (pos, normal=0, uv=0) like SceneManager::loadObject builds it (SceneManager.h:270-296)
+    std::vector<Vertex> verts(s.num_vertices());
+    for (uint32_t i = 0; i < s.num_vertices(); i++) {
+        verts[i].Position = CRT::Vec3(s.positions[3 * i], s.positions[3 * i + 1], s.positions[3 * i + 2]);
+        verts[i].Normal = CRT::Vec3(0.f);
+        verts[i].UV = CRT::Vec2(0.f);
+    }
+    // per-mesh contiguous vertex ranges + mesh-local indices
+    std::vector<uint32_t> localIdx(s.indices.size());
+    std::vector<uint32_t> vCount(w.numMeshes);
+    w.meshIndexOffset.resize(w.numMeshes);
+    w.meshIndexCount.resize(w.numMeshes);
+    w.meshVertexOffset.resize(w.numMeshes);
+    for (int m = 0; m < w.numMeshes; m++) {
+        uint32_t t0 = s.mesh_tri_offset[m], t1 = s.mesh_tri_offset[m + 1];
+        uint32_t vmin = 0xffffffffu, vmax = 0;
+        for (uint32_t i = 3 * t0; i < 3 * t1; i++) { vmin = std::min(vmin, s.indices[i]); vmax = std::max(vmax, s.indices[i]); }
+        if (t1 == t0) { vmin = 0; vmax = 0; }
+        for (uint32_t i = 3 * t0; i < 3 * t1; i++) localIdx[i] = s.indices[i] - vmin;
+        w.meshVertexOffset[m] = vmin;
+        vCount[m] = (t1 > t0) ? (vmax - vmin + 1) : 0;
+        w.meshIndexOffset[m] = 3 * t0;
+        w.meshIndexCount[m] = 3 * (t1 - t0);
+    }
+    if (!verts.empty()) {
+        CK(cudaMalloc(&w.dVertices, verts.size() * sizeof(Vertex)));
+        CK(cudaMemcpy(w.dVertices, verts.data(), verts.size() * sizeof(Vertex), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&w.dIndices, localIdx.size() * sizeof(uint32_t)));
+        CK(cudaMemcpy(w.dIndices, localIdx.data(), localIdx.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&w.dFaceMat, s.tri_material.size() * sizeof(int)));
+        CK(cudaMemcpy(w.dFaceMat, s.tri_material.data(), s.tri_material.size() * sizeof(int), cudaMemcpyHostToDevice));
+    }
+    if (w.numMeshes > 0) CK(cudaMalloc(&w.dMeshes, w.numMeshes * sizeof(CRT::Mesh)));
+    auto t0 = clk::now();
+    for (int m = 0; m < w.numMeshes; m++) {
+        CUDAKernels::initMesh CUDA_KERNEL(1, 1)(w.dMeshes + m, w.dVertices, w.dIndices, w.dFaceMat, vCount[m],
+                                                w.meshIndexCount[m], w.meshVertexOffset[m], w.meshIndexOffset[m],
+                                                w.meshIndexOffset[m] / 3, 0u, dRand);
+        CK(cudaGetLastError());
+        CK(cudaDeviceSynchronize());
+    }
+    auto t1 = clk::now();
+    w.mesh_build_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+
+    // MaterialData table. createRandomWorld appends the ground + metal materials itself, so
+    // when it is used the scene's last two materials (identical values) are not uploaded.
+    bool useCreateRandomWorld = (sceneName != "spheres");
+    size_t nMat = s.materials.size() - (useCreateRandomWorld ? 2 : 0);
+    std::vector<CRT::MaterialData> mats;
+    for (size_t i = 0; i < nMat; i++) {
+        const crt_material& m = s.materials[i];
+        mats.emplace_back((CRT::MaterialType)m.type, CRT::Vec3(m.albedo[0], m.albedo[1], m.albedo[2]), m.roughness, m.ior,
+                          CRT::Vec3(m.emission[0], m.emission[1], m.emission[2]));
+    }
+    if (!mats.empty()) {
+        CK(cudaMalloc(&w.dMats, mats.size() * sizeof(CRT::MaterialData)));
+        CK(cudaMemcpy(w.dMats, mats.data(), mats.size() * sizeof(CRT::MaterialData), cudaMemcpyHostToDevice));
+    }
+    t0 = clk::now();
+    if (useCreateRandomWorld) {
+        CUDAKernels::createRandomWorld CUDA_KERNEL(1, 1)(w.dWorld, w.dMeshes, w.numMeshes, w.dMats, (int)mats.size(), dObjectsNum, dRand);
+    } else {
+        float* dS = nullptr; int* dSM = nullptr;
+        CK(cudaMalloc(&dS, s.spheres.size() * sizeof(float)));
+        CK(cudaMemcpy(dS, s.spheres.data(), s.spheres.size() * sizeof(float), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&dSM, s.sphere_material.size() * sizeof(int)));
+        CK(cudaMemcpy(dSM, s.sphere_material.data(), s.sphere_material.size() * sizeof(int), cudaMemcpyHostToDevice));
+        shimCreateWorld CUDA_KERNEL(1, 1)(w.dWorld, w.dMeshes, w.numMeshes, w.dMats, (int)mats.size(), dS, dSM, (int)s.num_spheres(), dObjectsNum);
+    }
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
+    t1 = clk::now();
+    w.world_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    w.numObjects = *dObjectsNum;
+    int maxNodes = 2 * w.numObjects - 1;
+    CK(cudaMalloc(&w.dNodes, maxNodes * sizeof(CRT::BVHNode)));
+    t0 = clk::now();
+    CUDAKernels::createBVH CUDA_KERNEL(1, 1)(w.dWorld, w.dNodes, dRand);
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
+    t1 = clk::now();
+    w.top_bvh_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+}
+
+static bool parse_args(int argc, char** argv, Args& a) {
+    for (int i = 1; i < argc; i++) {
+        std::string k = argv[i];
+        auto need = [&](const char* name) -> const char* {
+            if (i + 1 >= argc) { fprintf(stderr, "missing value for %s\n", name); exit(2); }
+            return argv[++i];
+        };
+        if (k == "--scene") a.scene = need("--scene");
+        else if (k == "--param") a.param = atoi(need("--param"));
+        else if (k == "--width") a.width = atoi(need("--width"));
+        else if (k == "--height") a.height = atoi(need("--height"));
+        else if (k == "--spp") a.spp = atoi(need("--spp"));
+        else if (k == "--frames") a.frames = atoi(need("--frames"));
+        else if (k == "--warmup") a.warmup = atoi(need("--warmup"));
+        else if (k == "--seed") a.seed = strtoull(need("--seed"), nullptr, 10);
+        else if (k == "--dump") a.dump = need("--dump");
+        else if (k == "--twin") a.twin = true;
+        else if (k == "--primary") a.primary = true;
+        else if (k == "--rngkat") a.rngkat = true;
+        else if (k == "--stack") a.stack = atoi(need("--stack"));
+        else if (k == "--cam") { a.cam[0] = (float)atof(need("--cam")); a.cam[1] = (float)atof(need("--cam")); a.cam[2] = (float)atof(need("--cam")); }
+        else if (k == "--yaw") a.yaw = (float)atof(need("--yaw"));
+        else if (k == "--pitch") a.pitch = (float)atof(need("--pitch"));
+        else if (k == "--vfov") a.vfov = (float)atof(need("--vfov"));
+        else if (k == "--aperture") a.aperture = (float)atof(need("--aperture"));
+        else if (k == "--focus") a.focus = (float)atof(need("--focus"));
+        else if (k == "--aspect") a.aspect = (float)atof(need("--aspect"));
+        else { fprintf(stderr, "unknown argument %s\n", k.c_str()); return false; }
+    }
+    return true;
+}
+
+int main(int argc, char** argv) {
+    Args a;
+    if (!parse_args(argc, argv, a)) return 2;
+    try {
+        crt::SceneData scene;
+        crt_camera cam;
+        if (!crt::make_builtin_scene(a.scene, a.param, scene, cam)) {
+            fprintf(stderr, "unknown scene %s\n", a.scene.c_str());
+            return 2;
+        }
+        if (!std::isnan(a.cam[0])) { cam.position[0] = a.cam[0]; cam.position[1] = a.cam[1]; cam.position[2] = a.cam[2]; }
+        if (!std::isnan(a.yaw)) cam.yaw_deg = a.yaw;
+        if (!std::isnan(a.pitch)) cam.pitch_deg = a.pitch;
+        if (!std::isnan(a.vfov)) cam.vfov_deg = a.vfov;
+        if (!std::isnan(a.aperture)) cam.aperture = a.aperture;
+        if (!std::isnan(a.focus)) cam.focus_dist = a.focus;
+        if (!std::isnan(a.aspect)) cam.aspect = a.aspect;
+
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, 0));
+        // device heap: Mesh::buildBVHMesh news (2T-1) BVHNodes of 72 B (Mesh.cuh:123-124); the
+        // default 8 MB is too small for 69k triangles and upstream's own cudaDeviceSetLimit
+        // calls are commented out (EntryPoint.cu:23-26).
+        size_t heap = (size_t)64 << 20;
+        heap += (size_t)(2ull * scene.num_triangles() + 16) * sizeof(CRT::BVHNode) * 5 / 4;
+        CK(cudaDeviceSetLimit(cudaLimitMallocHeapSize, heap));
+        CK(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)a.stack));
+
+        const int W = a.width, H = a.height;
+        // RNG-known-answer dump does not need a scene
+        if (a.rngkat && !a.dump.empty()) {
+            std::vector<unsigned long long> seeds = {1804289383ull, 1804289383ull, 1804289383ull, 0ull, 1804289383ull, 12345678901234567ull};
+            std::vector<unsigned long long> subs = {0ull, 1ull, 65535ull, 0ull, 3686399ull, 29491199ull};
+            int cases = (int)seeds.size(), n = 16;
+            unsigned long long *dSeeds, *dSubs; unsigned int *dState, *dRaw; float* dUni;
+            CK(cudaMalloc(&dSeeds, cases * 8)); CK(cudaMalloc(&dSubs, cases * 8));
+            CK(cudaMalloc(&dState, cases * 6 * 4)); CK(cudaMalloc(&dRaw, cases * n * 4)); CK(cudaMalloc(&dUni, cases * n * 4));
+            CK(cudaMemcpy(dSeeds, seeds.data(), cases * 8, cudaMemcpyHostToDevice));
+            CK(cudaMemcpy(dSubs, subs.data(), cases * 8, cudaMemcpyHostToDevice));
+            shimRngKat<<<1, 32>>>(dSeeds, dSubs, cases, n, dState, dRaw, dUni);
+            CK(cudaGetLastError()); CK(cudaDeviceSynchronize());
+            std::vector<unsigned int> st(cases * 6), raw(cases * n); std::vector<float> uni(cases * n);
+            CK(cudaMemcpy(st.data(), dState, st.size() * 4, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(raw.data(), dRaw, raw.size() * 4, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(uni.data(), dUni, uni.size() * 4, cudaMemcpyDeviceToHost));
+            std::string p = a.dump + "_rngkat.txt";
+            FILE* f = fopen(p.c_str(), "w");
+            if (!f) throw std::runtime_error("cannot write " + p);
+            for (int c = 0; c < cases; c++) {
+                fprintf(f, "case %llu %llu\nstate", seeds[c], subs[c]);
+                for (int k = 0; k < 6; k++) fprintf(f, " %u", st[c * 6 + k]);
+                fprintf(f, "\nraw");
+                for (int i = 0; i < n; i++) fprintf(f, " %u", raw[c * n + i]);
+                fprintf(f, "\nuniform_bits");
+                for (int i = 0; i < n; i++) { uint32_t b; memcpy(&b, &uni[c * n + i], 4); fprintf(f, " %u", b); }
+                fprintf(f, "\n");
+            }
+            fclose(f);
+        }
+
+        // ---- the reference's own host objects ------------------------------------------
+        CUDAHelpers::RenderConfig cfg = CUDAHelpers::createRenderConfig(W, H);
+        CUDARenderer renderer(W, H);
+        // CUDARenderer::initialize seeds with rand() (CUDARenderer.cuh:46); do the same two
+        // cudaMallocs + launch here with an explicit seed so runs are reproducible.
+        renderer.m_RenderConfig = cfg;
+        CK(cudaMalloc(&renderer.m_dImageData, (size_t)W * H * 4));
+        CK(cudaMalloc(&renderer.m_dRandState, (size_t)cfg.totalThreads * sizeof(curandState)));
+        cudaEvent_t e0, e1;
+        CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+        auto init_rng = [&]() {
+            CK(cudaEventRecord(e0));
+            CUDAKernels::initRandState CUDA_KERNEL(cfg.blocks, cfg.threads)(renderer.m_dRandState, a.seed, W, H);
+            CK(cudaGetLastError());
+            CK(cudaEventRecord(e1));
+            CK(cudaDeviceSynchronize());
+            float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+            return ms;
+        };
+        float rng_ms = init_rng();
+
+        World world;
+        build_world(scene, a.scene, renderer.getRandState(), world);
+
+        // camera: the reference ctor (Camera.cuh:18-30) + yaw/pitch, then updateCameraVectors
+        CRT::Camera camera(cam.aspect, cam.vfov_deg, CRT::Vec3(cam.position[0], cam.position[1], cam.position[2]),
+                           CRT::Vec3(0, 0, 0), CRT::Vec3(cam.world_up[0], cam.world_up[1], cam.world_up[2]),
+                           cam.aperture, cam.focus_dist);
+        camera.m_Yaw = cam.yaw_deg;
+        camera.m_Pitch = cam.pitch_deg;
+        camera.updateCameraVectors();
+        camera.m_SamplesPerPixel = a.spp;
+        camera.m_PixelSampleScale = 1.f / camera.m_SamplesPerPixel;   // Camera.cuh:71
+        renderer.updateCamera(camera);
+
+        // ---- untimed twin first (fresh RNG), so its ray count refers to frame 0 -----------
+        unsigned long long rays = 0;
+        int twin_matches = -1;
+        std::vector<unsigned char> twinImg;
+        if (a.twin) {
+            float* dRad; unsigned long long* dCount; unsigned char* dImg2;
+            CK(cudaMalloc(&dRad, (size_t)W * H * 3 * sizeof(float)));
+            CK(cudaMalloc(&dCount, 8)); CK(cudaMemset(dCount, 0, 8));
+            CK(cudaMalloc(&dImg2, (size_t)W * H * 4));
+            shimRenderTwin CUDA_KERNEL(cfg.blocks, cfg.threads)(dImg2, dRad, dCount, world.dNodes, world.dWorld, renderer.m_dRandState, W, H);
+            CK(cudaGetLastError()); CK(cudaDeviceSynchronize());
+            CK(cudaMemcpy(&rays, dCount, 8, cudaMemcpyDeviceToHost));
+            twinImg.resize((size_t)W * H * 4);
+            CK(cudaMemcpy(twinImg.data(), dImg2, twinImg.size(), cudaMemcpyDeviceToHost));
+            if (!a.dump.empty()) {
+                std::vector<float> rad((size_t)W * H * 3);
+                CK(cudaMemcpy(rad.data(), dRad, rad.size() * sizeof(float), cudaMemcpyDeviceToHost));
+                write_bin(a.dump + "_radiance_f32.bin", rad.data(), rad.size() * sizeof(float));
+            }
+            cudaFree(dRad); cudaFree(dCount); cudaFree(dImg2);
+            rng_ms = init_rng();   // rewind the streams for the timed frames
+        }
+
+        // ---- timed frames: the reference's own CUDARenderer::render -----------------------
+        std::vector<float> frame_ms;
+        for (int f = 0; f < a.warmup + a.frames; f++) {
+            CK(cudaEventRecord(e0));
+            renderer.render(world.dNodes, world.dWorld);
+            CK(cudaEventRecord(e1));
+            CK(cudaEventSynchronize(e1));
+            float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+            if (f >= a.warmup) frame_ms.push_back(ms);
+            if (f == 0) {
+                std::vector<unsigned char> img((size_t)W * H * 4);
+                CK(cudaMemcpy(img.data(), renderer.getImageData(), img.size(), cudaMemcpyDeviceToHost));
+                if (!a.dump.empty()) write_bin(a.dump + "_rgba8.bin", img.data(), img.size());
+                if (a.twin) twin_matches = (img == twinImg) ? 1 : 0;
+            }
+        }
+
+        // ---- primary-hit dump ---------------------------------------------------------------
+        if (a.primary && !a.dump.empty()) {
+            int *dObj, *dPos; float* dT;
+            CK(cudaMalloc(&dObj, (size_t)W * H * 4)); CK(cudaMalloc(&dPos, (size_t)W * H * 4)); CK(cudaMalloc(&dT, (size_t)W * H * 4));
+            shimPrimaryDump CUDA_KERNEL(cfg.blocks, cfg.threads)(dObj, dPos, dT, world.dNodes, world.dWorld, world.numMeshes, a.seed, W, H);
+            CK(cudaGetLastError()); CK(cudaDeviceSynchronize());
+            std::vector<int> obj((size_t)W * H), pos((size_t)W * H); std::vector<float> tt((size_t)W * H);
+            CK(cudaMemcpy(obj.data(), dObj, obj.size() * 4, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(pos.data(), dPos, pos.size() * 4, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(tt.data(), dT, tt.size() * 4, cudaMemcpyDeviceToHost));
+            // permuted index array -> original triangle ids (unique vertex triplets per mesh)
+            std::vector<uint32_t> permIdx(scene.indices.size());
+            if (!permIdx.empty()) CK(cudaMemcpy(permIdx.data(), world.dIndices, permIdx.size() * 4, cudaMemcpyDeviceToHost));
+            std::vector<int> permToOrig(scene.num_triangles(), -1);
+            for (int m = 0; m < world.numMeshes; m++) {
+                std::map<std::array<uint32_t, 3>, int> lut;
+                uint32_t t0 = scene.mesh_tri_offset[m], t1 = scene.mesh_tri_offset[m + 1];
+                for (uint32_t t = t0; t < t1; t++)
+                    lut[{scene.indices[3 * t] - world.meshVertexOffset[m], scene.indices[3 * t + 1] - world.meshVertexOffset[m],
+                         scene.indices[3 * t + 2] - world.meshVertexOffset[m]}] = (int)t;
+                for (uint32_t t = t0; t < t1; t++) {
+                    auto it = lut.find({permIdx[3 * t], permIdx[3 * t + 1], permIdx[3 * t + 2]});
+                    permToOrig[t] = (it == lut.end()) ? -1 : it->second;
+                }
+            }
+            std::vector<int> ids((size_t)W * H);
+            for (size_t p = 0; p < ids.size(); p++) {
+                if (obj[p] < 0) ids[p] = -1;
+                else if (obj[p] < world.numMeshes) ids[p] = permToOrig[scene.mesh_tri_offset[obj[p]] + pos[p]];
+                else ids[p] = (int)scene.num_triangles() + (obj[p] - world.numMeshes);
+            }
+            write_bin(a.dump + "_primid_i32.bin", ids.data(), ids.size() * 4);
+            write_bin(a.dump + "_primt_f32.bin", tt.data(), tt.size() * 4);
+            write_bin(a.dump + "_perm_i32.bin", permToOrig.data(), permToOrig.size() * 4);
+            cudaFree(dObj); cudaFree(dPos); cudaFree(dT);
+        }
+
+        double sum = 0, mn = 1e30, mx = 0;
+        for (float m : frame_ms) { sum += m; mn = std::min(mn, (double)m); mx = std::max(mx, (double)m); }
+        double mean = frame_ms.empty() ? 0.0 : sum / frame_ms.size();
+        printf("{\"impl\": \"reference\", \"scene\": \"%s\", \"param\": %d, \"width\": %d, \"height\": %d, \"spp\": %d, "
+               "\"max_bounces\": %d, \"seed\": %llu, \"frames\": %d, \"warmup\": %d, \"frame_ms_mean\": %.4f, "
+               "\"frame_ms_min\": %.4f, \"frame_ms_max\": %.4f, \"rays_frame0\": %llu, \"twin_matches_render\": %d, "
+               "\"rng_init_ms\": %.3f, \"mesh_bvh_build_ms\": %.3f, \"world_ms\": %.3f, \"top_bvh_ms\": %.3f, "
+               "\"triangles\": %u, \"spheres\": %u, \"objects\": %d, \"gpu\": \"%s\", \"stack_bytes\": %d}\n",
+               a.scene.c_str(), a.param, W, H, a.spp, (int)REF_MAX_BOUNCES, a.seed, a.frames, a.warmup, mean,
+               frame_ms.empty() ? 0.0 : mn, mx, rays, twin_matches, rng_ms, world.mesh_build_ms, world.world_ms,
+               world.top_bvh_ms, scene.num_triangles(), scene.num_spheres(), world.numObjects, prop.name, a.stack);
+        fflush(stdout);
+        return 0;
+    } catch (const std::exception& e) {
+        fprintf(stderr, "ref_render: %s\n", e.what());
+        return 1;
+    }
+}
