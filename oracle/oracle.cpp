@@ -823,4 +823,17 @@ void orc_camera_vectors(const crt_camera* cam, float out[19]) {
     out[18] = k.lens_radius;
 }
 
+void orc_rng_states(uint64_t seed, uint64_t subseq_base, int W, int H, int threads, uint32_t* out6) {
+    xw_sequence_table();
+    parallel_rows(H, threads, [&](int y) {
+        Xorwow first{};
+        for (int x = 0; x < W; x++) {
+            size_t pix = (size_t)y * W + x;
+            if (x == 0) first = xorwow_init(seed, subseq_base + pix);
+            else xw_apply(xw_sequence_table()[0], first.v);
+            store_state(out6 + pix * 6, first);
+        }
+    });
+}
+
 }  // extern "C"

@@ -1,0 +1,350 @@
+// crt_api.cu — the C-ABI of include/crt_api.h: context, scene upload, camera, render, read-back.
+//
+// Host-side replacement for CUDARenderer + the device half of SceneManager
+// (reference: CudaRayTracer/src/CUDARenderer.cuh:9-60, src/SceneManager.h:61-98).
+// No CPU fallback: every entry point that needs the GPU fails with CRT_E_NO_DEVICE / CRT_E_CUDA.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/crt_api.h"
+#include "crt_camera_host.h"
+#include "crt_internal.h"
+#include "crt_trace.h"
+#include "scene_gen.h"
+
+using namespace crt;
+
+struct crt_ctx {
+    crt_config cfg{};
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // frame buffers
+    FrameBuffers fb{};
+    bool rng_ready = false;
+    // scene
+    float* d_pos = nullptr;
+    uint32_t* d_idx = nullptr;
+    int32_t* d_trimat = nullptr;
+    float* d_sph = nullptr;
+    int32_t* d_sphmat = nullptr;
+    MatRec* d_mats = nullptr;
+    uint32_t num_mats = 0;
+    WideBvh bvh{};
+    bool scene_ready = false;
+    Camera cam{};
+    bool cam_ready = false;
+    WavefrontState* wf = nullptr;
+    crt_stats stats{};
+    std::string err;
+};
+
+static std::string g_create_error = "";
+
+static int fail(crt_ctx* ctx, int code, const std::string& msg) {
+    if (ctx) ctx->err = msg; else g_create_error = msg;
+    return code;
+}
+static int fail_cuda(crt_ctx* ctx, cudaError_t e, const char* what) {
+    (void)cudaGetLastError();
+    return fail(ctx, CRT_E_CUDA, std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")");
+}
+#define CU(call)                                                        \
+    do {                                                                \
+        cudaError_t e__ = (call);                                       \
+        if (e__ != cudaSuccess) return fail_cuda(ctx, e__, #call);      \
+    } while (0)
+
+static void free_scene(crt_ctx* ctx) {
+    cudaFree(ctx->d_pos); cudaFree(ctx->d_idx); cudaFree(ctx->d_trimat); cudaFree(ctx->d_sph); cudaFree(ctx->d_sphmat);
+    cudaFree(ctx->d_mats); cudaFree(ctx->bvh.nodes); cudaFree(ctx->bvh.prims);
+    ctx->d_pos = nullptr; ctx->d_idx = nullptr; ctx->d_trimat = nullptr; ctx->d_sph = nullptr; ctx->d_sphmat = nullptr;
+    ctx->d_mats = nullptr; ctx->bvh = WideBvh(); ctx->scene_ready = false;
+}
+
+static SceneView scene_view(const crt_ctx* ctx) {
+    SceneView v;
+    v.nodes = ctx->bvh.nodes; v.prims = ctx->bvh.prims; v.mats = ctx->d_mats;
+    v.num_mats = ctx->num_mats; v.num_nodes = ctx->bvh.num_nodes; v.num_prims = ctx->bvh.num_prims;
+    return v;
+}
+
+extern "C" {
+
+int crt_api_version(void) { return CRT_API_VERSION; }
+
+// internal helpers for crt_host.cpp / crt_obj.cpp (not declared in the public header)
+int crt_ctx_size_(const crt_ctx* ctx, int* w, int* h) {
+    if (!ctx) return CRT_E_INVALID;
+    *w = ctx->cfg.width;
+    *h = ctx->cfg.height;
+    return CRT_OK;
+}
+int crt_ctx_fail_(crt_ctx* ctx, int code, const char* msg) { return fail(ctx, code, msg ? msg : ""); }
+
+const char* crt_last_error(const crt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int crt_create(crt_ctx** out_ctx, const crt_config* cfg) {
+    crt_ctx* ctx = nullptr;   // for the CU macro: errors before allocation go to the global message
+    if (!out_ctx || !cfg) return fail(nullptr, CRT_E_INVALID, "crt_create: null argument");
+    *out_ctx = nullptr;
+    if (cfg->width <= 0 || cfg->height <= 0 || (long long)cfg->width * cfg->height > (1ll << 30))
+        return fail(nullptr, CRT_E_INVALID, "crt_create: bad image size");
+    if (cfg->mode != CRT_MODE_WAVEFRONT && cfg->mode != CRT_MODE_MEGAKERNEL) return fail(nullptr, CRT_E_INVALID, "crt_create: bad mode");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0) { (void)cudaGetLastError(); return fail(nullptr, CRT_E_NO_DEVICE, "crt_create: no CUDA device (this library has no CPU fallback)"); }
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(nullptr, CRT_E_INVALID, "crt_create: bad device ordinal");
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major != 10) return fail(nullptr, CRT_E_NO_DEVICE, std::string("crt_create: kernels are built for sm_100a only, device is ") + prop.name);
+    CU(cudaSetDevice(cfg->device));
+    ctx = new (std::nothrow) crt_ctx();
+    if (!ctx) return fail(nullptr, CRT_E_NOMEM, "crt_create: out of host memory");
+    ctx->cfg = *cfg;
+    if (ctx->cfg.bvh_leaf_max <= 0) ctx->cfg.bvh_leaf_max = 3;
+    ctx->num_sms = prop.multiProcessorCount;
+    const size_t n = (size_t)cfg->width * cfg->height;
+    cudaError_t e2 = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e2 == cudaSuccess) e2 = cudaEventCreate(&ctx->ev0);
+    if (e2 == cudaSuccess) e2 = cudaEventCreate(&ctx->ev1);
+    if (e2 == cudaSuccess) e2 = cudaMalloc(&ctx->fb.rng, n * 6 * sizeof(uint32_t));
+    if (e2 == cudaSuccess) e2 = cudaMalloc(&ctx->fb.accum, n * sizeof(float4));
+    if (e2 == cudaSuccess) e2 = cudaMalloc(&ctx->fb.rgba8, n * sizeof(uint32_t));
+    if (e2 == cudaSuccess) e2 = cudaMalloc(&ctx->fb.counters, 8 * sizeof(unsigned long long));
+    if (e2 == cudaSuccess) e2 = cudaMemsetAsync(ctx->fb.accum, 0, n * sizeof(float4), ctx->stream);
+    if (e2 == cudaSuccess) e2 = cudaMemsetAsync(ctx->fb.rgba8, 0, n * sizeof(uint32_t), ctx->stream);
+    if (e2 == cudaSuccess && cfg->mode == CRT_MODE_WAVEFRONT) e2 = wavefront_create(&ctx->wf, cfg->width, cfg->height);
+    if (e2 == cudaSuccess) e2 = cudaStreamSynchronize(ctx->stream);
+    if (e2 != cudaSuccess) {
+        int rc = fail_cuda(nullptr, e2, "crt_create: allocation");
+        crt_destroy(ctx);
+        return rc;
+    }
+    *out_ctx = ctx;
+    return CRT_OK;
+}
+
+void crt_destroy(crt_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->cfg.device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    free_scene(ctx);
+    wavefront_destroy(ctx->wf);
+    cudaFree(ctx->fb.rng); cudaFree(ctx->fb.accum); cudaFree(ctx->fb.rgba8); cudaFree(ctx->fb.counters);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    (void)cudaGetLastError();
+    delete ctx;
+}
+
+int crt_init_rng(crt_ctx* ctx, uint64_t seed, uint64_t subsequence_base) {
+    if (!ctx) return CRT_E_INVALID;
+    CU(cudaSetDevice(ctx->cfg.device));
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    CU(launch_rng_init(ctx->fb.rng, ctx->cfg.width, ctx->cfg.height, seed, subsequence_base, ctx->num_sms, ctx->stream));
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaEventElapsedTime(&ctx->stats.rng_init_ms, ctx->ev0, ctx->ev1));
+    ctx->rng_ready = true;
+    return CRT_OK;
+}
+
+int crt_set_scene(crt_ctx* ctx, const crt_scene* sc) {
+    if (!ctx || !sc) return ctx ? fail(ctx, CRT_E_INVALID, "crt_set_scene: null scene") : CRT_E_INVALID;
+    const uint32_t T = sc->num_triangles, S = sc->num_spheres;
+    if (T + S == 0) return fail(ctx, CRT_E_INVALID, "crt_set_scene: empty scene");
+    if (T && (!sc->positions || !sc->indices || !sc->tri_material || sc->num_vertices == 0))
+        return fail(ctx, CRT_E_INVALID, "crt_set_scene: triangles without vertex/index/material arrays");
+    if (S && (!sc->spheres || !sc->sphere_material)) return fail(ctx, CRT_E_INVALID, "crt_set_scene: spheres without arrays");
+    if (sc->num_materials && !sc->materials) return fail(ctx, CRT_E_INVALID, "crt_set_scene: null materials");
+    for (size_t i = 0; i < (size_t)3 * T; i++)
+        if (sc->indices[i] >= sc->num_vertices) return fail(ctx, CRT_E_INVALID, "crt_set_scene: vertex index out of range");
+    CU(cudaSetDevice(ctx->cfg.device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    free_scene(ctx);
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    if (T) {
+        CU(cudaMalloc(&ctx->d_pos, (size_t)sc->num_vertices * 3 * sizeof(float)));
+        CU(cudaMalloc(&ctx->d_idx, (size_t)T * 3 * sizeof(uint32_t)));
+        CU(cudaMalloc(&ctx->d_trimat, (size_t)T * sizeof(int32_t)));
+        CU(cudaMemcpyAsync(ctx->d_pos, sc->positions, (size_t)sc->num_vertices * 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->d_idx, sc->indices, (size_t)T * 3 * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->d_trimat, sc->tri_material, (size_t)T * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (S) {
+        CU(cudaMalloc(&ctx->d_sph, (size_t)S * 4 * sizeof(float)));
+        CU(cudaMalloc(&ctx->d_sphmat, (size_t)S * sizeof(int32_t)));
+        CU(cudaMemcpyAsync(ctx->d_sph, sc->spheres, (size_t)S * 4 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->d_sphmat, sc->sphere_material, (size_t)S * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    std::vector<MatRec> mats;
+    for (uint32_t i = 0; i < sc->num_materials; i++) mats.push_back(make_mat_record(sc->materials[i]));
+    ctx->num_mats = sc->num_materials;
+    CU(cudaMalloc(&ctx->d_mats, (mats.size() ? mats.size() : 1) * sizeof(MatRec)));
+    if (!mats.empty()) CU(cudaMemcpyAsync(ctx->d_mats, mats.data(), mats.size() * sizeof(MatRec), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaEventElapsedTime(&ctx->stats.scene_upload_ms, ctx->ev0, ctx->ev1));
+
+    SceneInput in;
+    in.positions = ctx->d_pos; in.indices = ctx->d_idx; in.tri_material = ctx->d_trimat;
+    in.spheres = ctx->d_sph; in.sphere_material = ctx->d_sphmat; in.num_triangles = T; in.num_spheres = S;
+    cudaError_t ce = cudaSuccess;
+    int rc = build_bvh_device(in, (uint32_t)ctx->cfg.bvh_leaf_max, ctx->stream, ctx->num_sms, ctx->bvh, &ctx->stats.bvh_build_ms, &ce);
+    if (rc != CRT_OK) {
+        free_scene(ctx);
+        if (ce != cudaSuccess) return fail_cuda(ctx, ce, "crt_set_scene: BVH build");
+        return fail(ctx, rc, "crt_set_scene: BVH build failed");
+    }
+    if (2 * ctx->bvh.depth + 2 > CRT_STACK_ENTRIES) {
+        free_scene(ctx);
+        return fail(ctx, CRT_E_LIMIT, "crt_set_scene: BVH too deep for the traversal stack");
+    }
+    ctx->stats.bvh_nodes = ctx->bvh.num_nodes;
+    ctx->stats.bvh_prims = ctx->bvh.num_prims;
+    ctx->stats.bvh_depth = ctx->bvh.depth;
+    ctx->scene_ready = true;
+    return CRT_OK;
+}
+
+int crt_set_camera(crt_ctx* ctx, const crt_camera* cam) {
+    if (!ctx || !cam) return ctx ? fail(ctx, CRT_E_INVALID, "crt_set_camera: null camera") : CRT_E_INVALID;
+    ctx->cam = make_camera(*cam);
+    ctx->cam_ready = true;
+    return CRT_OK;
+}
+
+static int render_impl(crt_ctx* ctx, const crt_render_params* p, bool counted) {
+    if (!ctx || !p) return ctx ? fail(ctx, CRT_E_INVALID, "crt_render: null params") : CRT_E_INVALID;
+    if (!ctx->scene_ready) return fail(ctx, CRT_E_INVALID, "crt_render: no scene (call crt_set_scene)");
+    if (!ctx->cam_ready) return fail(ctx, CRT_E_INVALID, "crt_render: no camera (call crt_set_camera)");
+    if (!ctx->rng_ready) return fail(ctx, CRT_E_INVALID, "crt_render: RNG not initialised (call crt_init_rng)");
+    if (p->spp <= 0 || p->spp >= (1 << 24) || p->max_bounces <= 0 || p->max_bounces > 255 || p->min_bounces < 1)
+        return fail(ctx, CRT_E_INVALID, "crt_render: need 0 < spp < 2^24, 0 < max_bounces <= 255, min_bounces >= 1");
+    CU(cudaSetDevice(ctx->cfg.device));
+    RenderArgs a;
+    a.scene = scene_view(ctx);
+    a.cam = ctx->cam;
+    a.rc.width = ctx->cfg.width; a.rc.height = ctx->cfg.height; a.rc.spp = p->spp;
+    a.rc.max_bounces = p->max_bounces; a.rc.min_bounces = p->min_bounces; a.rc.rr_max_prob = p->rr_max_prob;
+    a.fb = ctx->fb;
+    a.flags = p->flags;
+    CU(cudaMemsetAsync(ctx->fb.counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    uint32_t launches = 0;
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    if (ctx->cfg.mode == CRT_MODE_MEGAKERNEL) CU(launch_render_mega(a, counted, ctx->num_sms, ctx->stream, &launches));
+    else CU(launch_render_wavefront(ctx->wf, a, counted, ctx->num_sms, ctx->stream, &launches));
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    unsigned long long c[4] = {0, 0, 0, 0};
+    CU(cudaMemcpyAsync(c, ctx->fb.counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaEventElapsedTime(&ctx->stats.render_ms, ctx->ev0, ctx->ev1));
+    ctx->stats.rays = c[0];
+    ctx->stats.rays_total += c[0];
+    ctx->stats.samples = (uint64_t)ctx->cfg.width * ctx->cfg.height * (uint64_t)p->spp;
+    ctx->stats.nodes_fetched = c[2];
+    ctx->stats.prims_tested = c[3];
+    ctx->stats.kernel_launches = launches;
+    return CRT_OK;
+}
+
+int crt_render(crt_ctx* ctx, const crt_render_params* p) { return render_impl(ctx, p, false); }
+int crt_render_counted(crt_ctx* ctx, const crt_render_params* p) { return render_impl(ctx, p, true); }
+
+int crt_primary_ids(crt_ctx* ctx, uint64_t seed, uint64_t subsequence_base, int32_t* out_ids, float* out_t) {
+    if (!ctx || !out_ids) return ctx ? fail(ctx, CRT_E_INVALID, "crt_primary_ids: null output") : CRT_E_INVALID;
+    if (!ctx->scene_ready || !ctx->cam_ready) return fail(ctx, CRT_E_INVALID, "crt_primary_ids: scene and camera must be set");
+    CU(cudaSetDevice(ctx->cfg.device));
+    const size_t n = (size_t)ctx->cfg.width * ctx->cfg.height;
+    int32_t* d_ids = nullptr;
+    float* d_t = nullptr;
+    CU(cudaMalloc(&d_ids, n * sizeof(int32_t)));
+    cudaError_t e = out_t ? cudaMalloc(&d_t, n * sizeof(float)) : cudaSuccess;
+    if (e == cudaSuccess) e = launch_primary(scene_view(ctx), ctx->cam, ctx->cfg.width, ctx->cfg.height, seed, subsequence_base, d_ids, d_t, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_ids, d_ids, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && out_t) e = cudaMemcpyAsync(out_t, d_t, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_ids);
+    cudaFree(d_t);
+    if (e != cudaSuccess) return fail_cuda(ctx, e, "crt_primary_ids");
+    return CRT_OK;
+}
+
+int crt_get_image_rgba8(crt_ctx* ctx, void* host, void** out_dev) {
+    if (!ctx) return CRT_E_INVALID;
+    CU(cudaSetDevice(ctx->cfg.device));
+    if (out_dev) *out_dev = ctx->fb.rgba8;
+    if (host) {
+        CU(cudaMemcpyAsync(host, ctx->fb.rgba8, (size_t)ctx->cfg.width * ctx->cfg.height * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    return CRT_OK;
+}
+
+int crt_get_accum(crt_ctx* ctx, float* host, void** out_dev) {
+    if (!ctx) return CRT_E_INVALID;
+    CU(cudaSetDevice(ctx->cfg.device));
+    if (out_dev) *out_dev = ctx->fb.accum;
+    if (host) {
+        CU(cudaMemcpyAsync(host, ctx->fb.accum, (size_t)ctx->cfg.width * ctx->cfg.height * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    return CRT_OK;
+}
+
+int crt_set_accum(crt_ctx* ctx, const float* host) {
+    if (!ctx || !host) return ctx ? fail(ctx, CRT_E_INVALID, "crt_set_accum: null buffer") : CRT_E_INVALID;
+    CU(cudaSetDevice(ctx->cfg.device));
+    CU(cudaMemcpyAsync(ctx->fb.accum, host, (size_t)ctx->cfg.width * ctx->cfg.height * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return CRT_OK;
+}
+
+int crt_tonemap(crt_ctx* ctx) {
+    if (!ctx) return CRT_E_INVALID;
+    CU(cudaSetDevice(ctx->cfg.device));
+    CU(launch_tonemap(ctx->fb, ctx->cfg.width, ctx->cfg.height, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return CRT_OK;
+}
+
+int crt_get_rng_state(crt_ctx* ctx, uint32_t* host, void** out_dev) {
+    if (!ctx) return CRT_E_INVALID;
+    CU(cudaSetDevice(ctx->cfg.device));
+    if (out_dev) *out_dev = ctx->fb.rng;
+    if (host) {
+        CU(cudaMemcpyAsync(host, ctx->fb.rng, (size_t)ctx->cfg.width * ctx->cfg.height * 6 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    return CRT_OK;
+}
+
+int crt_set_rng_state(crt_ctx* ctx, const uint32_t* host) {
+    if (!ctx || !host) return ctx ? fail(ctx, CRT_E_INVALID, "crt_set_rng_state: null buffer") : CRT_E_INVALID;
+    CU(cudaSetDevice(ctx->cfg.device));
+    CU(cudaMemcpyAsync(ctx->fb.rng, host, (size_t)ctx->cfg.width * ctx->cfg.height * 6 * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->rng_ready = true;
+    return CRT_OK;
+}
+
+int crt_get_stats(crt_ctx* ctx, crt_stats* out) {
+    if (!ctx || !out) return CRT_E_INVALID;
+    *out = ctx->stats;
+    return CRT_OK;
+}
+
+int crt_get_stream(crt_ctx* ctx, void** out_stream) {
+    if (!ctx || !out_stream) return CRT_E_INVALID;
+    *out_stream = (void*)ctx->stream;
+    return CRT_OK;
+}
+
+}  // extern "C"

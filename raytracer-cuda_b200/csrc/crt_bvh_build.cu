@@ -1,0 +1,104 @@
+// crt_bvh_build.cu — CUDA execution policy for the BVH build (sm_100a).
+//
+// One kernel launch per build step (grid-stride over the items, grid sized in multiples of the SM
+// count), cub::DeviceRadixSort for the Morton order, cub::DeviceScan for the PLOC compaction.
+// Replaces the reference's <<<1,1>>> builders (reference: CudaRayTracer/src/CUDAKernels.h:86-100).
+#include <cuda_runtime.h>
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+#include "crt_bvh_driver.h"
+#include "crt_internal.h"
+
+namespace crt {
+
+template <class F>
+__global__ void __launch_bounds__(256) k_for_n(int n, F f) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) f(i);
+}
+
+struct CudaExec {
+    cudaStream_t stream;
+    int num_sms;
+    cudaError_t err = cudaSuccess;
+    void* cub_tmp = nullptr;
+    size_t cub_tmp_bytes = 0;
+
+    void note(cudaError_t e) { if (err == cudaSuccess && e != cudaSuccess) err = e; }
+
+    template <class T> T* alloc(size_t n) {
+        void* p = nullptr;
+        cudaError_t e = cudaMalloc(&p, (n ? n : 1) * sizeof(T));
+        if (e != cudaSuccess) { note(e); return nullptr; }
+        return (T*)p;
+    }
+    void release(void* p) { if (p) note(cudaFree(p)); }
+
+    template <class F> void for_n(int n, const F& f) {
+        if (n <= 0) return;
+        int blocks = (n + 255) / 256;
+        const int cap = num_sms * 8;             // 8 resident 256-thread CTAs per SM
+        if (blocks > cap) blocks = cap;
+        k_for_n<F><<<blocks, 256, 0, stream>>>(n, f);
+        note(cudaGetLastError());
+    }
+
+    void ensure_tmp(size_t bytes) {
+        if (bytes <= cub_tmp_bytes) return;
+        if (cub_tmp) cudaFree(cub_tmp);
+        cub_tmp = nullptr;
+        cub_tmp_bytes = 0;
+        if (cudaMalloc(&cub_tmp, bytes) == cudaSuccess) cub_tmp_bytes = bytes;
+        else note(cudaErrorMemoryAllocation);
+    }
+
+    void sort_pairs(uint64_t* keys, uint32_t* vals, uint64_t* keys_tmp, uint32_t* vals_tmp, int n, uint64_t** ks, uint32_t** vs) {
+        size_t bytes = 0;
+        note(cub::DeviceRadixSort::SortPairs(nullptr, bytes, keys, keys_tmp, vals, vals_tmp, n, 0, 63, stream));
+        ensure_tmp(bytes);
+        if (cub_tmp) note(cub::DeviceRadixSort::SortPairs(cub_tmp, bytes, keys, keys_tmp, vals, vals_tmp, n, 0, 63, stream));
+        *ks = keys_tmp;
+        *vs = vals_tmp;
+    }
+
+    void exclusive_scan(const uint32_t* in, uint32_t* out, int n) {
+        size_t bytes = 0;
+        note(cub::DeviceScan::ExclusiveSum(nullptr, bytes, in, out, n, stream));
+        ensure_tmp(bytes);
+        if (cub_tmp) note(cub::DeviceScan::ExclusiveSum(cub_tmp, bytes, in, out, n, stream));
+    }
+
+    void upload(void* d, const void* s, size_t b) {
+        note(cudaMemcpyAsync(d, s, b, cudaMemcpyHostToDevice, stream));
+        note(cudaStreamSynchronize(stream));   // the source is usually a stack temporary
+    }
+    void download(void* d, const void* s, size_t b) {
+        note(cudaMemcpyAsync(d, s, b, cudaMemcpyDeviceToHost, stream));
+        note(cudaStreamSynchronize(stream));
+    }
+};
+
+int build_bvh_device(const SceneInput& dev_in, uint32_t leaf_max, cudaStream_t stream, int num_sms, WideBvh& out,
+                     float* build_ms, cudaError_t* cuda_err) {
+    CudaExec ex;
+    ex.stream = stream;
+    ex.num_sms = num_sms > 0 ? num_sms : 148;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaEventRecord(e0, stream);
+    int rc = build_wide_bvh(ex, dev_in, leaf_max, out);
+    cudaEventRecord(e1, stream);
+    ex.note(cudaStreamSynchronize(stream));
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, e0, e1) != cudaSuccess) ms = 0.f;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (ex.cub_tmp) cudaFree(ex.cub_tmp);
+    if (build_ms) *build_ms = ms;
+    if (cuda_err) *cuda_err = ex.err;
+    if (ex.err != cudaSuccess) return CRT_E_CUDA;
+    return rc;
+}
+
+}  // namespace crt

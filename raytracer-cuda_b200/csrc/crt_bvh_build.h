@@ -1,0 +1,415 @@
+// crt_bvh_build.h — parallel BVH build: Morton order -> PLOC binary BVH -> 8-wide compressed BVH.
+//
+// Replaces the reference's two single-GPU-thread builders
+// (reference: CudaRayTracer/src/Core/Mesh.cuh:121-219 Mesh::buildBVHMesh,
+//  Core/BVHNode.cuh:21-84 BVHNode::buildBVHScene, launched <<<1,1>>> from src/SceneManager.h:95,180).
+//
+// Every step is a data-parallel functor `void operator()(int i)` run over n items by an execution
+// policy. The product library instantiates the builder with the CUDA policy (crt_bvh_build.cu:
+// one kernel launch per step, cub radix sort / scan). tests/hostsim instantiates the same functors
+// with a sequential host policy to debug the algorithm without a GPU — test infrastructure only.
+//
+// Algorithm
+//   1. primitive boxes + centroid bounds                      (PrimBoxFn)
+//   2. 63-bit Morton codes of the centroids, radix sort       (MortonFn, Exec::sort_pairs)
+//   3. PLOC (Meister & Bittner 2018): repeat { nearest neighbour within +-R along the Morton
+//      order by surface area of the union; merge mutual pairs; compact } until one cluster
+//   4. collapse to 8-wide nodes level by level: greedy largest-area expansion, leaves of <=
+//      leaf_max primitives, octant-ordered child slots, 8-bit quantised child boxes
+//      (Ylitie, Karras, Laine 2017), primitive records written in leaf order.
+#pragma once
+#include "crt_types.h"
+
+namespace crt {
+
+#if defined(__CUDA_ARCH__)
+CRT_HD uint32_t atomic_add_u32(uint32_t* p, uint32_t v) { return atomicAdd(p, v); }
+CRT_HD void atomic_min_i32(int32_t* p, int32_t v) { atomicMin(p, v); }
+CRT_HD void atomic_max_i32(int32_t* p, int32_t v) { atomicMax(p, v); }
+#else
+CRT_HD uint32_t atomic_add_u32(uint32_t* p, uint32_t v) { uint32_t o = *p; *p = o + v; return o; }
+CRT_HD void atomic_min_i32(int32_t* p, int32_t v) { if (v < *p) *p = v; }
+CRT_HD void atomic_max_i32(int32_t* p, int32_t v) { if (v > *p) *p = v; }
+#endif
+
+// order-preserving float <-> int32 (for atomic min/max on floats)
+CRT_HD int32_t float_ordered(float f) { int32_t i = (int32_t)f_bits(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+CRT_HD float ordered_float(int32_t i) { return bits_f((uint32_t)(i >= 0 ? i : i ^ 0x7fffffff)); }
+
+struct SceneInput {   // device (or host-sim) pointers to the caller's flat arrays
+    const float* positions;
+    const uint32_t* indices;
+    const int32_t* tri_material;
+    const float* spheres;
+    const int32_t* sphere_material;
+    uint32_t num_triangles;
+    uint32_t num_spheres;
+};
+
+CRT_HD float fmin3(float a, float b, float c) { return fminf(a, fminf(b, c)); }
+CRT_HD float fmax3(float a, float b, float c) { return fmaxf(a, fmaxf(b, c)); }
+
+// next representable float towards -inf / +inf (finite inputs)
+CRT_HD float f_down(float x) { uint32_t u = f_bits(x); if (x > 0.f) u--; else if (x < 0.f) u++; else u = 0x80000001u; return bits_f(u); }
+CRT_HD float f_up(float x) { uint32_t u = f_bits(x); if (x > 0.f) u++; else if (x < 0.f) u--; else u = 0x00000001u; return bits_f(u); }
+
+// ---- step 1: primitive boxes ------------------------------------------------------------
+struct PrimBoxFn {
+    SceneInput in;
+    f4* plo;            // per primitive (lo.xyz, -)
+    f4* phi;            // per primitive (hi.xyz, -)
+    int32_t* cbounds;   // centroid bounds, float_ordered: min xyz, max xyz
+    CRT_HD void operator()(int i) const {
+        float lx, ly, lz, hx, hy, hz;
+        if ((uint32_t)i < in.num_triangles) {
+            const uint32_t a = in.indices[3 * i], b = in.indices[3 * i + 1], c = in.indices[3 * i + 2];
+            const float ax = in.positions[3 * a], ay = in.positions[3 * a + 1], az = in.positions[3 * a + 2];
+            const float bx = in.positions[3 * b], by = in.positions[3 * b + 1], bz = in.positions[3 * b + 2];
+            const float cx = in.positions[3 * c], cy = in.positions[3 * c + 1], cz = in.positions[3 * c + 2];
+            lx = fmin3(ax, bx, cx); ly = fmin3(ay, by, cy); lz = fmin3(az, bz, cz);
+            hx = fmax3(ax, bx, cx); hy = fmax3(ay, by, cy); hz = fmax3(az, bz, cz);
+        } else {
+            const uint32_t j = (uint32_t)i - in.num_triangles;
+            const float cx = in.spheres[4 * j], cy = in.spheres[4 * j + 1], cz = in.spheres[4 * j + 2];
+            const float r = fabsf(in.spheres[4 * j + 3]);
+            // c -/+ r rounds to nearest; step one ulp outwards so the box contains the sphere
+            lx = f_down(cx - r); ly = f_down(cy - r); lz = f_down(cz - r);
+            hx = f_up(cx + r); hy = f_up(cy + r); hz = f_up(cz + r);
+        }
+        f4 lo; lo.x = lx; lo.y = ly; lo.z = lz; lo.w = 0.f;
+        f4 hi; hi.x = hx; hi.y = hy; hi.z = hz; hi.w = 0.f;
+        plo[i] = lo;
+        phi[i] = hi;
+        const float mx = 0.5f * (lx + hx), my = 0.5f * (ly + hy), mz = 0.5f * (lz + hz);
+        atomic_min_i32(&cbounds[0], float_ordered(mx));
+        atomic_min_i32(&cbounds[1], float_ordered(my));
+        atomic_min_i32(&cbounds[2], float_ordered(mz));
+        atomic_max_i32(&cbounds[3], float_ordered(mx));
+        atomic_max_i32(&cbounds[4], float_ordered(my));
+        atomic_max_i32(&cbounds[5], float_ordered(mz));
+    }
+};
+
+// ---- step 2: Morton codes -----------------------------------------------------------------
+CRT_HD uint64_t spread21(uint32_t v) {   // 21 bits -> every third bit of 63
+    uint64_t x = v & 0x1fffffu;
+    x = (x | (x << 32)) & 0x1f00000000ffffull;
+    x = (x | (x << 16)) & 0x1f0000ff0000ffull;
+    x = (x | (x << 8)) & 0x100f00f00f00f00full;
+    x = (x | (x << 4)) & 0x10c30c30c30c30c3ull;
+    x = (x | (x << 2)) & 0x1249249249249249ull;
+    return x;
+}
+
+struct MortonFn {
+    const f4* plo;
+    const f4* phi;
+    const int32_t* cbounds;
+    uint64_t* keys;
+    uint32_t* vals;
+    CRT_HD void operator()(int i) const {
+        const float bx = ordered_float(cbounds[0]), by = ordered_float(cbounds[1]), bz = ordered_float(cbounds[2]);
+        const float ex = ordered_float(cbounds[3]) - bx, ey = ordered_float(cbounds[4]) - by, ez = ordered_float(cbounds[5]) - bz;
+        const float mx = 0.5f * (plo[i].x + phi[i].x), my = 0.5f * (plo[i].y + phi[i].y), mz = 0.5f * (plo[i].z + phi[i].z);
+        const float scale = 2097151.0f;
+        const float nx = ex > 0.f ? (mx - bx) / ex : 0.f, ny = ey > 0.f ? (my - by) / ey : 0.f, nz = ez > 0.f ? (mz - bz) / ez : 0.f;
+        const uint32_t qx = (uint32_t)fminf(fmaxf(nx * scale, 0.f), scale);
+        const uint32_t qy = (uint32_t)fminf(fmaxf(ny * scale, 0.f), scale);
+        const uint32_t qz = (uint32_t)fminf(fmaxf(nz * scale, 0.f), scale);
+        keys[i] = (spread21(qx) << 2) | (spread21(qy) << 1) | spread21(qz);
+        vals[i] = (uint32_t)i;
+    }
+};
+
+// ---- binary BVH storage: node k box = (blo[k].xyz, bhi[k].xyz); blo[k].w = left child,
+// bhi[k].w = right child (as uint bits). Leaf: left = 0xffffffff, right = primitive number.
+// Nodes [0,N) are the leaves in Morton order, inner nodes are appended from N.
+CRT_HD f4 mk_f4(float x, float y, float z, uint32_t wbits) { f4 r; r.x = x; r.y = y; r.z = z; r.w = bits_f(wbits); return r; }
+
+struct InitLeavesFn {
+    const f4* plo;
+    const f4* phi;
+    const uint32_t* sorted_prim;
+    f4* blo;
+    f4* bhi;
+    uint32_t* bcount;
+    uint32_t* cluster;
+    CRT_HD void operator()(int i) const {
+        const uint32_t p = sorted_prim[i];
+        blo[i] = mk_f4(plo[p].x, plo[p].y, plo[p].z, 0xffffffffu);
+        bhi[i] = mk_f4(phi[p].x, phi[p].y, phi[p].z, p);
+        bcount[i] = 1u;
+        cluster[i] = (uint32_t)i;
+    }
+};
+
+
+// ---- step 3: PLOC ---------------------------------------------------------------------------
+#ifndef CRT_PLOC_RADIUS
+#define CRT_PLOC_RADIUS 24
+#endif
+
+CRT_HD float union_area(const f4& alo, const f4& ahi, const f4& blo_, const f4& bhi_) {
+    const float ex = fmaxf(ahi.x, bhi_.x) - fminf(alo.x, blo_.x);
+    const float ey = fmaxf(ahi.y, bhi_.y) - fminf(alo.y, blo_.y);
+    const float ez = fmaxf(ahi.z, bhi_.z) - fminf(alo.z, blo_.z);
+    return ex * ey + ey * ez + ez * ex;
+}
+
+// nearest neighbour of cluster i among clusters [i-R, i+R]; ties -> smallest index (this makes
+// the lexicographically smallest closest pair mutual, so every round merges at least one pair)
+struct PlocNearestFn {
+    const f4* blo;
+    const f4* bhi;
+    const uint32_t* cluster;
+    uint32_t* nearest;
+    int n;
+    CRT_HD void operator()(int i) const {
+        const uint32_t ci = cluster[i];
+        const f4 lo = blo[ci], hi = bhi[ci];
+        const int j0 = i - CRT_PLOC_RADIUS < 0 ? 0 : i - CRT_PLOC_RADIUS;
+        const int j1 = i + CRT_PLOC_RADIUS > n - 1 ? n - 1 : i + CRT_PLOC_RADIUS;
+        float best = INFINITY;
+        int bj = -1;
+        for (int j = j0; j <= j1; j++) {
+            if (j == i) continue;
+            const uint32_t cj = cluster[j];
+            const float a = union_area(lo, hi, blo[cj], bhi[cj]);
+            if (a < best || bj < 0) { best = a; bj = j; }
+        }
+        nearest[i] = (uint32_t)bj;
+    }
+};
+
+// merge mutual nearest pairs; merged[i] = new cluster id, 0xffffffff when i was absorbed
+struct PlocMergeFn {
+    f4* blo;
+    f4* bhi;
+    uint32_t* bcount;
+    const uint32_t* cluster;
+    const uint32_t* nearest;
+    uint32_t* merged;
+    uint32_t* flags;
+    uint32_t* node_counter;   // number of binary nodes allocated so far
+    CRT_HD void operator()(int i) const {
+        const uint32_t j = nearest[i];
+        uint32_t out = cluster[i];
+        if (nearest[j] == (uint32_t)i) {
+            if ((uint32_t)i < j) {
+                const uint32_t a = cluster[i], b = cluster[j];
+                const uint32_t id = atomic_add_u32(node_counter, 1u);
+                const f4 alo = blo[a], ahi = bhi[a], blo_ = blo[b], bhi_ = bhi[b];
+                blo[id] = mk_f4(fminf(alo.x, blo_.x), fminf(alo.y, blo_.y), fminf(alo.z, blo_.z), a);
+                bhi[id] = mk_f4(fmaxf(ahi.x, bhi_.x), fmaxf(ahi.y, bhi_.y), fmaxf(ahi.z, bhi_.z), b);
+                bcount[id] = bcount[a] + bcount[b];
+                out = id;
+            } else {
+                out = 0xffffffffu;
+            }
+        }
+        merged[i] = out;
+        flags[i] = out != 0xffffffffu ? 1u : 0u;
+    }
+};
+
+// scatter survivors to their scanned positions (keeps Morton order); item n-1 publishes the total
+struct PlocCompactFn {
+    const uint32_t* merged;
+    const uint32_t* flags;
+    const uint32_t* pos;      // exclusive scan of flags
+    uint32_t* cluster_out;
+    uint32_t* total;
+    int n;
+    CRT_HD void operator()(int i) const {
+        if (flags[i]) cluster_out[pos[i]] = merged[i];
+        if (i == n - 1) *total = pos[i] + flags[i];
+    }
+};
+
+
+// ---- step 4: collapse to the 8-wide compressed layout ---------------------------------------
+CRT_HD float box_half_area(const f4& lo, const f4& hi) {
+    const float ex = hi.x - lo.x, ey = hi.y - lo.y, ez = hi.z - lo.z;
+    return ex * ey + ey * ez + ez * ex;
+}
+
+// exponent byte e such that 2^(e-127) * 255 >= extent  (0 for a zero extent: scale 0)
+CRT_HD uint32_t quant_exponent(float extent) {
+    if (!(extent > 0.f)) return 0u;
+    int e;
+    const double m = frexp((double)extent / 255.0, &e);   // extent/255 = m * 2^e, m in [0.5,1)
+    if (m == 0.5) e -= 1;                                  // exact power of two
+    int biased = e + 127;
+    if (biased < 1) biased = 1;
+    if (biased > 254) biased = 254;
+    return (uint32_t)biased;
+}
+
+CRT_HD PrimRec make_prim_record(const SceneInput& in, uint32_t p) {
+    PrimRec r;
+    if (p < in.num_triangles) {
+        const uint32_t a = in.indices[3 * p], b = in.indices[3 * p + 1], c = in.indices[3 * p + 2];
+        const vec3 v0 = mk3(in.positions[3 * a], in.positions[3 * a + 1], in.positions[3 * a + 2]);
+        const vec3 v1 = mk3(in.positions[3 * b], in.positions[3 * b + 1], in.positions[3 * b + 2]);
+        const vec3 v2 = mk3(in.positions[3 * c], in.positions[3 * c + 1], in.positions[3 * c + 2]);
+        const vec3 e1 = v_sub(v1, v0), e2 = v_sub(v2, v0);   // Mesh.cuh:277-278
+        r.q0.x = v0.x; r.q0.y = v0.y; r.q0.z = v0.z; r.q0.w = e1.x;
+        r.q1.x = e1.y; r.q1.y = e1.z; r.q1.z = e2.x; r.q1.w = e2.y;
+        r.q2.x = e2.z; r.q2.y = bits_f(p); r.q2.z = bits_f((uint32_t)in.tri_material[p]); r.q2.w = bits_f((uint32_t)PRIM_TRIANGLE);
+    } else {
+        const uint32_t j = p - in.num_triangles;
+        const float rad = in.spheres[4 * j + 3];
+        r.q0.x = in.spheres[4 * j]; r.q0.y = in.spheres[4 * j + 1]; r.q0.z = in.spheres[4 * j + 2]; r.q0.w = rad;
+        r.q1.x = f_mul(rad, rad); r.q1.y = 0.f; r.q1.z = 0.f; r.q1.w = 0.f;   // m_RadSquared, Sphere.cuh:12
+        r.q2.x = 0.f; r.q2.y = bits_f(p); r.q2.z = bits_f((uint32_t)in.sphere_material[j]); r.q2.w = bits_f((uint32_t)PRIM_SPHERE);
+    }
+    return r;
+}
+
+struct CollapseFn {
+    const f4* blo;
+    const f4* bhi;
+    const uint32_t* bcount;
+    SceneInput in;
+    WideNode* nodes;
+    PrimRec* prims;
+    uint32_t* wide_bnode;    // binary node collapsed into wide node k
+    uint32_t* counters;      // [0] wide nodes allocated, [1] primitive records allocated
+    uint32_t level_begin;
+    uint32_t leaf_max;       // <= 3
+
+    CRT_HD uint32_t left_of(uint32_t b) const { return f_bits(blo[b].w); }
+    CRT_HD uint32_t right_of(uint32_t b) const { return f_bits(bhi[b].w); }
+
+    CRT_HD void operator()(int k) const {
+        const uint32_t w = level_begin + (uint32_t)k;
+        const uint32_t b = wide_bnode[w];
+        uint32_t ch[8];
+        int nch;
+        if (bcount[b] <= leaf_max) {          // tiny scene: the root itself is one leaf
+            ch[0] = b;
+            nch = 1;
+        } else {
+            ch[0] = left_of(b);
+            ch[1] = right_of(b);
+            nch = 2;
+            while (nch < 8) {                 // open the largest inner child until 8 children
+                int best = -1;
+                float best_area = -1.f;
+                for (int i = 0; i < nch; i++) {
+                    if (bcount[ch[i]] <= leaf_max) continue;
+                    const float a = box_half_area(blo[ch[i]], bhi[ch[i]]);
+                    if (a > best_area) { best_area = a; best = i; }
+                }
+                if (best < 0) break;
+                const uint32_t c = ch[best];
+                ch[best] = left_of(c);
+                ch[nch++] = right_of(c);
+            }
+        }
+        // node frame
+        const f4 nlo = blo[b], nhi = bhi[b];
+        const uint32_t ex = quant_exponent(nhi.x - nlo.x), ey = quant_exponent(nhi.y - nlo.y), ez = quant_exponent(nhi.z - nlo.z);
+        const double scx = ex ? ldexp(1.0, (int)ex - 127) : 0.0, scy = ey ? ldexp(1.0, (int)ey - 127) : 0.0, scz = ez ? ldexp(1.0, (int)ez - 127) : 0.0;
+        const float ncx = 0.5f * (nlo.x + nhi.x), ncy = 0.5f * (nlo.y + nhi.y), ncz = 0.5f * (nlo.z + nhi.z);
+
+        // greedy child -> slot assignment: slot s is visited first by rays whose direction sign
+        // per axis is + where bit (4,2,1) of s is 0, so it should hold the child lying furthest
+        // towards - on those axes: cost(c,s) = dot(centroid_c - centroid_node, sign(s))
+        int slot_child[8];
+        for (int s = 0; s < 8; s++) slot_child[s] = -1;
+        bool used[8];
+        for (int i = 0; i < 8; i++) used[i] = false;
+        float cost[8][8];
+        for (int i = 0; i < nch; i++) {
+            const f4 lo = blo[ch[i]], hi = bhi[ch[i]];
+            const float dx = 0.5f * (lo.x + hi.x) - ncx, dy = 0.5f * (lo.y + hi.y) - ncy, dz = 0.5f * (lo.z + hi.z) - ncz;
+            for (int s = 0; s < 8; s++) {
+                const float sxn = (s & 4) ? 1.f : -1.f, syn = (s & 2) ? 1.f : -1.f, szn = (s & 1) ? 1.f : -1.f;
+                cost[i][s] = dx * sxn + dy * syn + dz * szn;
+            }
+        }
+        for (int it = 0; it < nch; it++) {
+            float bc = -INFINITY;
+            int bi = -1, bs = -1;
+            for (int i = 0; i < nch; i++) {
+                if (used[i]) continue;
+                for (int s = 0; s < 8; s++) {
+                    if (slot_child[s] >= 0) continue;
+                    if (bi < 0 || cost[i][s] > bc) { bc = cost[i][s]; bi = i; bs = s; }
+                }
+            }
+            used[bi] = true;
+            slot_child[bs] = bi;
+        }
+        // allocate children
+        uint32_t n_inner = 0, n_prims = 0;
+        for (int i = 0; i < nch; i++) {
+            if (bcount[ch[i]] <= leaf_max) n_prims += bcount[ch[i]];
+            else n_inner++;
+        }
+        const uint32_t child_base = n_inner ? atomic_add_u32(&counters[0], n_inner) : 0u;
+        const uint32_t prim_base = n_prims ? atomic_add_u32(&counters[1], n_prims) : 0u;
+
+        uint32_t imask = 0u;
+        uint32_t meta[8], qlx[8], qly[8], qlz[8], qhx[8], qhy[8], qhz[8];
+        uint32_t inner_rank = 0, prim_off = 0;
+        for (int s = 0; s < 8; s++) {
+            meta[s] = 0u;
+            qlx[s] = qly[s] = qlz[s] = 255u;      // empty slot: inverted box, never hit
+            qhx[s] = qhy[s] = qhz[s] = 0u;
+            const int i = slot_child[s];
+            if (i < 0) continue;
+            const uint32_t c = ch[i];
+            const f4 lo = blo[c], hi = bhi[c];
+            // exact in double: floor/ceil of (bound - p) / 2^e
+            double v;
+            v = scx > 0.0 ? floor(((double)lo.x - (double)nlo.x) / scx) : 0.0; qlx[s] = (uint32_t)(v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v));
+            v = scy > 0.0 ? floor(((double)lo.y - (double)nlo.y) / scy) : 0.0; qly[s] = (uint32_t)(v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v));
+            v = scz > 0.0 ? floor(((double)lo.z - (double)nlo.z) / scz) : 0.0; qlz[s] = (uint32_t)(v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v));
+            v = scx > 0.0 ? ceil(((double)hi.x - (double)nlo.x) / scx) : 0.0; qhx[s] = (uint32_t)(v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v));
+            v = scy > 0.0 ? ceil(((double)hi.y - (double)nlo.y) / scy) : 0.0; qhy[s] = (uint32_t)(v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v));
+            v = scz > 0.0 ? ceil(((double)hi.z - (double)nlo.z) / scz) : 0.0; qhz[s] = (uint32_t)(v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v));
+            if (bcount[c] > leaf_max) {
+                imask |= 1u << s;
+                meta[s] = (1u << 5) | (24u + (uint32_t)s);
+                wide_bnode[child_base + inner_rank] = c;
+                inner_rank++;
+            } else {
+                // gather the <= 3 primitives of this subtree (depth-first, left first)
+                const uint32_t cnt = bcount[c];
+                uint32_t st[4];
+                int sp = 0;
+                st[sp++] = c;
+                uint32_t written = 0;
+                while (sp > 0) {
+                    const uint32_t x = st[--sp];
+                    if (left_of(x) == 0xffffffffu) {
+                        prims[prim_base + prim_off + written] = make_prim_record(in, right_of(x));
+                        written++;
+                    } else {
+                        st[sp++] = right_of(x);
+                        st[sp++] = left_of(x);
+                    }
+                }
+                const uint32_t unary = cnt >= 3 ? 7u : (cnt == 2 ? 3u : 1u);
+                meta[s] = (unary << 5) | prim_off;
+                prim_off += cnt;
+            }
+        }
+        WideNode out;
+        out.n0.x = f_bits(nlo.x); out.n0.y = f_bits(nlo.y); out.n0.z = f_bits(nlo.z);
+        out.n0.w = ex | (ey << 8) | (ez << 16) | (imask << 24);
+        out.n1.x = child_base; out.n1.y = prim_base;
+        out.n1.z = meta[0] | (meta[1] << 8) | (meta[2] << 16) | (meta[3] << 24);
+        out.n1.w = meta[4] | (meta[5] << 8) | (meta[6] << 16) | (meta[7] << 24);
+#define CRT_PACK4(a, o) ((a)[o] | ((a)[o + 1] << 8) | ((a)[o + 2] << 16) | ((a)[o + 3] << 24))
+        out.n2.x = CRT_PACK4(qlx, 0); out.n2.y = CRT_PACK4(qlx, 4); out.n2.z = CRT_PACK4(qly, 0); out.n2.w = CRT_PACK4(qly, 4);
+        out.n3.x = CRT_PACK4(qlz, 0); out.n3.y = CRT_PACK4(qlz, 4); out.n3.z = CRT_PACK4(qhx, 0); out.n3.w = CRT_PACK4(qhx, 4);
+        out.n4.x = CRT_PACK4(qhy, 0); out.n4.y = CRT_PACK4(qhy, 4); out.n4.z = CRT_PACK4(qhz, 0); out.n4.w = CRT_PACK4(qhz, 4);
+#undef CRT_PACK4
+        nodes[w] = out;
+    }
+};
+
+}  // namespace crt

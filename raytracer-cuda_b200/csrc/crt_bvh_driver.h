@@ -1,0 +1,146 @@
+// crt_bvh_driver.h — orchestration of the BVH build steps over an execution policy.
+//
+// Exec must provide:
+//   template<class T> T* alloc(size_t n);   void release(void* p);
+//   template<class F> void for_n(int n, const F& f);          // run f(0..n-1) in parallel
+//   void sort_pairs(uint64_t* keys, uint32_t* vals, uint64_t* keys_tmp, uint32_t* vals_tmp, int n,
+//                   uint64_t** keys_sorted, uint32_t** vals_sorted);
+//   void exclusive_scan(const uint32_t* in, uint32_t* out, int n);
+//   void fill_u32(uint32_t* p, uint32_t v, size_t n);
+//   void upload(void* dst, const void* src, size_t bytes);    // host -> exec memory
+//   void download(void* dst, const void* src, size_t bytes);  // exec memory -> host (synchronises)
+// The product uses CudaExec (crt_bvh_build.cu); tests/hostsim uses a sequential HostExec.
+#pragma once
+#include "crt_bvh_build.h"
+
+namespace crt {
+
+struct WideBvh {
+    WideNode* nodes = nullptr;   // exec memory, num_nodes entries (capacity node_capacity)
+    PrimRec* prims = nullptr;    // exec memory, num_prims entries, leaf order
+    uint32_t num_nodes = 0;
+    uint32_t num_prims = 0;
+    uint32_t depth = 0;          // wide levels
+    uint32_t ploc_rounds = 0;
+};
+
+// Returns 0 on success, CRT_E_* otherwise. `in` points into exec memory.
+template <class Exec>
+int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& out) {
+    const uint32_t N = in.num_triangles + in.num_spheres;
+    if (N == 0) return CRT_E_INVALID;
+    if (N > 0x3fffffffu) return CRT_E_LIMIT;
+    if (leaf_max < 1) leaf_max = 1;
+    if (leaf_max > 3) leaf_max = 3;
+    const int n0 = (int)N;
+
+    f4* plo = ex.template alloc<f4>(N);
+    f4* phi = ex.template alloc<f4>(N);
+    int32_t* cbounds = ex.template alloc<int32_t>(6);
+    uint64_t* keys = ex.template alloc<uint64_t>(N);
+    uint64_t* keys_tmp = ex.template alloc<uint64_t>(N);
+    uint32_t* vals = ex.template alloc<uint32_t>(N);
+    uint32_t* vals_tmp = ex.template alloc<uint32_t>(N);
+    const size_t nb = (size_t)2 * N;   // 2N-1 binary nodes
+    f4* blo = ex.template alloc<f4>(nb);
+    f4* bhi = ex.template alloc<f4>(nb);
+    uint32_t* bcount = ex.template alloc<uint32_t>(nb);
+    uint32_t* cl_a = ex.template alloc<uint32_t>(N);
+    uint32_t* cl_b = ex.template alloc<uint32_t>(N);
+    uint32_t* nearest = ex.template alloc<uint32_t>(N);
+    uint32_t* merged = ex.template alloc<uint32_t>(N);
+    uint32_t* flags = ex.template alloc<uint32_t>(N);
+    uint32_t* pos = ex.template alloc<uint32_t>(N);
+    uint32_t* counters = ex.template alloc<uint32_t>(4);   // [0] wide nodes [1] prims [2] binary nodes [3] ploc total
+    if (!plo || !phi || !cbounds || !keys || !keys_tmp || !vals || !vals_tmp || !blo || !bhi || !bcount || !cl_a || !cl_b ||
+        !nearest || !merged || !flags || !pos || !counters)
+        return CRT_E_NOMEM;
+
+    // 1. boxes + centroid bounds
+    {
+        const int32_t init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int32_t)0x80000000, (int32_t)0x80000000, (int32_t)0x80000000};
+        ex.upload(cbounds, init, sizeof(init));
+        PrimBoxFn f;
+        f.in = in; f.plo = plo; f.phi = phi; f.cbounds = cbounds;
+        ex.for_n(n0, f);
+    }
+    // 2. Morton order
+    uint64_t* keys_sorted = keys;
+    uint32_t* vals_sorted = vals;
+    {
+        MortonFn f;
+        f.plo = plo; f.phi = phi; f.cbounds = cbounds; f.keys = keys; f.vals = vals;
+        ex.for_n(n0, f);
+        ex.sort_pairs(keys, vals, keys_tmp, vals_tmp, n0, &keys_sorted, &vals_sorted);
+    }
+    // 3. PLOC
+    {
+        InitLeavesFn f;
+        f.plo = plo; f.phi = phi; f.sorted_prim = vals_sorted; f.blo = blo; f.bhi = bhi; f.bcount = bcount; f.cluster = cl_a;
+        ex.for_n(n0, f);
+    }
+    {
+        const uint32_t init[4] = {1u, 0u, N, 0u};
+        ex.upload(counters, init, sizeof(init));
+    }
+    uint32_t* cl_in = cl_a;
+    uint32_t* cl_out = cl_b;
+    int n = n0;
+    uint32_t rounds = 0;
+    while (n > 1) {
+        PlocNearestFn fn;
+        fn.blo = blo; fn.bhi = bhi; fn.cluster = cl_in; fn.nearest = nearest; fn.n = n;
+        ex.for_n(n, fn);
+        PlocMergeFn fm;
+        fm.blo = blo; fm.bhi = bhi; fm.bcount = bcount; fm.cluster = cl_in; fm.nearest = nearest; fm.merged = merged;
+        fm.flags = flags; fm.node_counter = &counters[2];
+        ex.for_n(n, fm);
+        ex.exclusive_scan(flags, pos, n);
+        PlocCompactFn fc;
+        fc.merged = merged; fc.flags = flags; fc.pos = pos; fc.cluster_out = cl_out; fc.total = &counters[3]; fc.n = n;
+        ex.for_n(n, fc);
+        uint32_t total = 0;
+        ex.download(&total, &counters[3], sizeof(uint32_t));
+        if ((int)total >= n || total == 0) return CRT_E_CUDA;   // no progress: cannot happen (see PlocNearestFn)
+        n = (int)total;
+        uint32_t* t = cl_in; cl_in = cl_out; cl_out = t;
+        rounds++;
+    }
+    uint32_t root = 0;
+    ex.download(&root, cl_in, sizeof(uint32_t));
+
+    // 4. collapse. At most N-1 inner binary nodes -> at most max(N-1,1) wide nodes; N prim records.
+    const uint32_t node_cap = N > 1 ? N - 1 : 1;
+    out.nodes = ex.template alloc<WideNode>(node_cap);
+    out.prims = ex.template alloc<PrimRec>(N);
+    uint32_t* wide_bnode = ex.template alloc<uint32_t>(node_cap);
+    if (!out.nodes || !out.prims || !wide_bnode) return CRT_E_NOMEM;
+    ex.upload(wide_bnode, &root, sizeof(uint32_t));
+    uint32_t begin = 0, end = 1, depth = 0;
+    while (begin < end) {
+        CollapseFn f;
+        f.blo = blo; f.bhi = bhi; f.bcount = bcount; f.in = in; f.nodes = out.nodes; f.prims = out.prims;
+        f.wide_bnode = wide_bnode; f.counters = counters; f.level_begin = begin; f.leaf_max = leaf_max;
+        ex.for_n((int)(end - begin), f);
+        uint32_t c[2];
+        ex.download(c, counters, sizeof(c));
+        begin = end;
+        end = c[0];
+        out.num_prims = c[1];
+        depth++;
+        if (end > node_cap) return CRT_E_LIMIT;
+    }
+    out.num_nodes = end;
+    out.depth = depth;
+    out.ploc_rounds = rounds;
+
+    ex.release(wide_bnode);
+    ex.release(counters); ex.release(pos); ex.release(flags); ex.release(merged); ex.release(nearest);
+    ex.release(cl_b); ex.release(cl_a); ex.release(bcount); ex.release(bhi); ex.release(blo);
+    ex.release(vals_tmp); ex.release(vals); ex.release(keys_tmp); ex.release(keys);
+    ex.release(cbounds); ex.release(phi); ex.release(plo);
+    if (out.num_prims != N) return CRT_E_CUDA;
+    return CRT_OK;
+}
+
+}  // namespace crt

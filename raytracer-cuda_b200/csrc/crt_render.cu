@@ -1,0 +1,204 @@
+// crt_render.cu — RNG init, megakernel path tracer, primary-id pass, tonemap (sm_100a).
+//
+// Replaces CUDAKernels::initRandState and CUDAKernels::render
+// (reference: CudaRayTracer/src/CUDAKernels.h:18-26,147-166).
+#include <cuda_runtime.h>
+#include <curand_kernel.h>
+
+#include "crt_internal.h"
+#include "crt_shade.h"
+
+namespace crt {
+
+// Pixel owned by a thread: 16x16 pixel tile per 256-thread block, each warp an 8x4 sub-tile so the
+// 32 camera rays of a warp stay close together.
+__device__ __forceinline__ bool tile_pixel(int width, int height, int& x, int& y) {
+    const int tiles_x = (width + 15) >> 4;
+    const int bx = blockIdx.x % tiles_x, by = blockIdx.x / tiles_x;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    x = bx * 16 + (warp & 1) * 8 + (lane & 7);
+    y = by * 16 + (warp >> 1) * 4 + (lane >> 3);
+    return x < width && y < height;
+}
+
+// ---- RNG init: state[pixel] = curand_init(seed, subseq_base + pixel, 0) -----------------------
+// cuRAND's own device routine does the 2^67-per-subsequence skip-ahead; only v[0..4] and d are
+// kept (curand_uniform touches nothing else), as 6 coalesced planes instead of 48-byte AoS states.
+__global__ void __launch_bounds__(256) k_rng_init(uint32_t* planes, int width, int height, unsigned long long seed,
+                                                  unsigned long long base) {
+    const size_t n = (size_t)width * height;
+    for (size_t pix = (size_t)blockIdx.x * blockDim.x + threadIdx.x; pix < n; pix += (size_t)gridDim.x * blockDim.x) {
+        curandStateXORWOW_t st;
+        curand_init(seed, base + pix, 0, &st);
+        planes[pix] = st.v[0];
+        planes[n + pix] = st.v[1];
+        planes[2 * n + pix] = st.v[2];
+        planes[3 * n + pix] = st.v[3];
+        planes[4 * n + pix] = st.v[4];
+        planes[5 * n + pix] = st.d;
+    }
+}
+
+cudaError_t launch_rng_init(uint32_t* rng_planes, int width, int height, unsigned long long seed,
+                            unsigned long long subseq_base, int num_sms, cudaStream_t stream) {
+    const size_t n = (size_t)width * height;
+    int blocks = (int)((n + 255) / 256);
+    const int cap = num_sms * 8;
+    if (blocks > cap) blocks = cap;
+    k_rng_init<<<blocks, 256, 0, stream>>>(rng_planes, width, height, seed, subseq_base);
+    return cudaGetLastError();
+}
+
+__device__ __forceinline__ Rng load_rng(const uint32_t* planes, size_t n, size_t pix) {
+    Rng r;
+    r.v0 = planes[pix]; r.v1 = planes[n + pix]; r.v2 = planes[2 * n + pix];
+    r.v3 = planes[3 * n + pix]; r.v4 = planes[4 * n + pix]; r.d = planes[5 * n + pix];
+    return r;
+}
+__device__ __forceinline__ void store_rng(uint32_t* planes, size_t n, size_t pix, const Rng& r) {
+    planes[pix] = r.v0; planes[n + pix] = r.v1; planes[2 * n + pix] = r.v2;
+    planes[3 * n + pix] = r.v3; planes[4 * n + pix] = r.v4; planes[5 * n + pix] = r.d;
+}
+
+__device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ---- megakernel: one thread per pixel, all samples of the pixel in sequence --------------------
+// Same per-pixel work as CUDAKernels::render, restructured as a single loop with one traversal
+// call site: a lane whose path ended starts its next sample immediately, so every lane of a warp
+// has a ray in flight until its pixel is finished.
+template <bool COUNT>
+__global__ void __launch_bounds__(256) k_render_mega(RenderArgs a) {
+    int x, y;
+    const bool valid = tile_pixel(a.rc.width, a.rc.height, x, y);
+    unsigned long long rays = 0, nodes = 0, prims = 0;
+    if (valid) {
+        const size_t n = (size_t)a.rc.width * a.rc.height;
+        const size_t pix = (size_t)y * a.rc.width + x;
+        Rng rng = load_rng(a.fb.rng, n, pix);
+        vec3 sum = mk3(0.f, 0.f, 0.f);
+        float nprev = 0.f;
+        if (a.flags & CRT_RENDER_ACCUMULATE) {
+            const float4 acc = a.fb.accum[pix];
+            sum = mk3(acc.x, acc.y, acc.z);
+            nprev = acc.w;
+        }
+        TraceCounters ctr;
+        ctr.nodes = 0; ctr.prims = 0;
+        vec3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f), thr = mk3(1.f, 1.f, 1.f);
+        int sample = 0, bounce = 0;
+        bool alive = false;
+        uint32_t nrays = 0;
+        while (true) {
+            if (!alive) {
+                if (sample == a.rc.spp) break;
+                camera_ray(a.cam, x, y, a.rc.width, a.rc.height, rng, o, d);
+                thr = mk3(1.f, 1.f, 1.f);
+                bounce = 0;
+                alive = true;
+            }
+            if (bounce >= a.rc.min_bounces) {             // Russian roulette, CUDAKernels.h:113-121
+                const float p = fminf(fmaxf(thr.x, fmaxf(thr.y, thr.z)), a.rc.rr_max_prob);
+                if (rng_uniform(rng) > p) { alive = false; sample++; continue; }
+                thr = v_scale(thr, f_rcp(p));
+            }
+            HitRec h;
+            nrays++;
+            if (trace_closest<COUNT>(a.scene, o, d, 0.001f, INFINITY, h, &ctr)) {
+                const Surface s = surface_at(a.scene, h, o, d);
+                if (s.mat < a.scene.num_mats) {
+                    const MatRec m = a.scene.mats[s.mat];
+                    vec3 att, no, nd;
+                    if (scatter(m, s, d, rng, att, no, nd)) {
+                        thr = v_mul(thr, att);
+                        o = no;
+                        d = nd;
+                    } else {                               // raw emission ends the path, :132-134
+                        sum = v_add(sum, emitted(m));
+                        alive = false;
+                        sample++;
+                        continue;
+                    }
+                }
+            } else {                                       // sky, :137-142
+                sum = v_add(sum, v_mul(thr, background(d)));
+                alive = false;
+                sample++;
+                continue;
+            }
+            bounce++;
+            if (bounce >= a.rc.max_bounces) { alive = false; sample++; }   // exhausted: black
+        }
+        const float ntot = nprev + (float)a.rc.spp;
+        a.fb.accum[pix] = make_float4(sum.x, sum.y, sum.z, ntot);
+        if (!(a.flags & CRT_RENDER_NO_TONEMAP)) {
+            const float scale = f_div(1.f, ntot);          // m_PixelSampleScale, Camera.cuh:71
+            a.fb.rgba8[pix] = pack_rgba8(v_scale(sum, scale));
+        }
+        store_rng(a.fb.rng, n, pix, rng);
+        rays = nrays;
+        nodes = ctr.nodes;
+        prims = ctr.prims;
+    }
+    rays = warp_sum(rays);
+    if (COUNT) { nodes = warp_sum(nodes); prims = warp_sum(prims); }
+    if ((threadIdx.x & 31) == 0) {
+        if (rays) atomicAdd(&a.fb.counters[0], rays);
+        if (COUNT) { atomicAdd(&a.fb.counters[2], nodes); atomicAdd(&a.fb.counters[3], prims); }
+    }
+}
+
+cudaError_t launch_render_mega(const RenderArgs& a, bool counted, int num_sms, cudaStream_t stream, uint32_t* launches) {
+    (void)num_sms;
+    const int tiles = ((a.rc.width + 15) / 16) * ((a.rc.height + 15) / 16);
+    if (counted) k_render_mega<true><<<tiles, 256, 0, stream>>>(a);
+    else k_render_mega<false><<<tiles, 256, 0, stream>>>(a);
+    if (launches) *launches += 1;
+    return cudaGetLastError();
+}
+
+// ---- primary-hit ids (parity buffer) ----------------------------------------------------------
+__global__ void __launch_bounds__(256) k_primary(SceneView scene, Camera cam, int width, int height, unsigned long long seed,
+                                                 unsigned long long base, int32_t* ids, float* tout) {
+    int x, y;
+    if (!tile_pixel(width, height, x, y)) return;
+    const size_t pix = (size_t)y * width + x;
+    curandStateXORWOW_t st;
+    curand_init(seed, base + pix, 0, &st);
+    Rng rng;
+    rng.v0 = st.v[0]; rng.v1 = st.v[1]; rng.v2 = st.v[2]; rng.v3 = st.v[3]; rng.v4 = st.v[4]; rng.d = st.d;
+    vec3 o, d;
+    camera_ray(cam, x, y, width, height, rng, o, d);
+    HitRec h;
+    const bool hit = trace_closest<false>(scene, o, d, 0.001f, INFINITY, h, nullptr);
+    ids[pix] = hit ? h.id : -1;
+    if (tout) tout[pix] = hit ? h.t : INFINITY;
+}
+
+cudaError_t launch_primary(const SceneView& scene, const Camera& cam, int width, int height, unsigned long long seed,
+                           unsigned long long subseq_base, int32_t* ids, float* t, cudaStream_t stream) {
+    const int tiles = ((width + 15) / 16) * ((height + 15) / 16);
+    k_primary<<<tiles, 256, 0, stream>>>(scene, cam, width, height, seed, subseq_base, ids, t);
+    return cudaGetLastError();
+}
+
+// ---- tonemap: writeColor over the accumulation buffer (CRTUtility.cuh:21-32) -------------------
+__global__ void __launch_bounds__(256) k_tonemap(const float4* accum, uint32_t* rgba8, size_t n) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 a = accum[i];
+        const float scale = f_div(1.f, a.w);
+        rgba8[i] = a.w > 0.f ? pack_rgba8(v_scale(mk3(a.x, a.y, a.z), scale)) : 0xff000000u;
+    }
+}
+
+cudaError_t launch_tonemap(const FrameBuffers& fb, int width, int height, cudaStream_t stream) {
+    const size_t n = (size_t)width * height;
+    int blocks = (int)((n + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_tonemap<<<blocks, 256, 0, stream>>>(fb.accum, fb.rgba8, n);
+    return cudaGetLastError();
+}
+
+}  // namespace crt

@@ -1,0 +1,205 @@
+// crt_trace.h — closest-hit query: compressed 8-wide BVH traversal + primitive tests.
+//
+// Replaces BVHNode::hit -> virtual Mesh::hit / Sphere::hit -> AABB::hit
+// (reference: CudaRayTracer/src/Core/BVHNode.cuh:115-156, Core/Mesh.cuh:55-110,266-308,
+// Core/Sphere.cuh:18-47, Core/AABB.cuh:123-146).
+//
+// What must match the reference bit-for-bit is the set of accepted primitives and their t:
+//   - triangle: Moeller-Trumbore with eps 1e-8, inclusive edges, t in [tmin, closest]   (Mesh.cuh:266-293)
+//   - sphere  : half-b quadratic, nearer root in range else farther                     (Sphere.cuh:18-34)
+// both evaluated with the reference's compiled rounding sequence (crt_math.h).
+// Box tests only have to be conservative: a different BVH may visit primitives in a different
+// order, so the reference's "later equal-t hit replaces" (Mesh.cuh:293) is made order-independent
+// here: among equal t the larger primitive id wins.
+#pragma once
+#include "crt_types.h"
+
+namespace crt {
+
+struct HitRec {
+    float t;
+    uint32_t prim;   // index into SceneView::prims (leaf order)
+    int32_t id;      // caller's primitive id, -1 = miss
+};
+
+struct TraceCounters {
+    uint32_t nodes;
+    uint32_t prims;
+};
+
+#ifndef CRT_STACK_ENTRIES
+#define CRT_STACK_ENTRIES 48
+#endif
+
+#if defined(__CUDA_ARCH__)
+CRT_HD int hi_bit(uint32_t v) { return 31 - __clz((int)v); }
+CRT_HD int pop_count(uint32_t v) { return __popc(v); }
+CRT_HD f4 ld_f4(const f4* p) { float4 v = __ldg(reinterpret_cast<const float4*>(p)); f4 r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w; return r; }
+CRT_HD u4 ld_u4(const u4* p) { uint4 v = __ldg(reinterpret_cast<const uint4*>(p)); u4 r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w; return r; }
+#else
+CRT_HD int hi_bit(uint32_t v) { return 31 - __builtin_clz(v); }
+CRT_HD int pop_count(uint32_t v) { return __builtin_popcount(v); }
+CRT_HD f4 ld_f4(const f4* p) { return *p; }
+CRT_HD u4 ld_u4(const u4* p) { return *p; }
+#endif
+
+CRT_HD float byte_f(uint32_t w, int i) { return (float)((w >> (8 * i)) & 0xffu); }
+
+// Primitive test. Returns true when `rec` accepts the hit and updates rec / closest.
+CRT_HD bool test_prim(const PrimRec* prims, uint32_t index, vec3 o, vec3 d, float tmin, HitRec& rec) {
+    const f4 q0 = ld_f4(&prims[index].q0);
+    const f4 q1 = ld_f4(&prims[index].q1);
+    const f4 q2 = ld_f4(&prims[index].q2);
+    const int32_t id = (int32_t)f_bits(q2.y);
+    float t;
+    if (f_bits(q2.w) == (uint32_t)PRIM_TRIANGLE) {
+        // Mesh::rayTriangleIntersect, Mesh.cuh:266-293
+        const vec3 v0 = mk3(q0.x, q0.y, q0.z);
+        const vec3 e1 = mk3(q0.w, q1.x, q1.y);
+        const vec3 e2 = mk3(q1.z, q1.w, q2.x);
+        const vec3 h = v_cross(d, e2);
+        const float a = v_dot(e1, h);
+        if (fabsf(a) < 1e-8f) return false;
+        const float f = f_rcp(a);
+        const vec3 s = v_sub(o, v0);
+        const float u = f_mul(f, v_dot(s, h));
+        if (u < 0.f || u > 1.f) return false;
+        const vec3 q = v_cross(s, e1);
+        const float v = f_mul(f, v_dot(d, q));
+        if (v < 0.f || f_add(u, v) > 1.f) return false;
+        t = f_mul(f, v_dot(e2, q));
+        if (t < tmin || t > rec.t) return false;
+    } else {
+        // Sphere::hit, Sphere.cuh:18-34
+        const vec3 oc = v_sub(o, mk3(q0.x, q0.y, q0.z));
+        const float a = v_dot(d, d);
+        const float half_b = v_dot(oc, d);
+        const float c = f_sub(v_dot(oc, oc), q1.x);
+        const float disc = f_fma(half_b, half_b, -f_mul(a, c));
+        if (disc < 0.f) return false;
+        const float sq = f_sqrt(disc);
+        t = f_div(f_sub(-half_b, sq), a);
+        if (t < tmin || t > rec.t) {
+            t = f_div(f_sub(sq, half_b), a);
+            if (t < tmin || t > rec.t) return false;
+        }
+    }
+    if (t == rec.t && id < rec.id) return false;   // order-independent tie rule
+    rec.t = t;
+    rec.prim = index;
+    rec.id = id;
+    return true;
+}
+
+// Closest hit in [tmin, tmax]. COUNT switches the work counters on (crt_render_counted).
+template <bool COUNT>
+CRT_HD bool trace_closest(const SceneView& sc, vec3 o, vec3 d, float tmin, float tmax, HitRec& rec, TraceCounters* ctr) {
+    rec.t = tmax;
+    rec.prim = 0u;
+    rec.id = -1;
+
+    // reciprocal direction with zero components nudged (box tests only; primitive tests use d)
+    const float tiny = 1e-20f;
+    const float ddx = fabsf(d.x) < tiny ? (d.x < 0.f ? -tiny : tiny) : d.x;
+    const float ddy = fabsf(d.y) < tiny ? (d.y < 0.f ? -tiny : tiny) : d.y;
+    const float ddz = fabsf(d.z) < tiny ? (d.z < 0.f ? -tiny : tiny) : d.z;
+    const float idx = 1.0f / ddx, idy = 1.0f / ddy, idz = 1.0f / ddz;
+    const bool negx = ddx < 0.f, negy = ddy < 0.f, negz = ddz < 0.f;
+    const uint32_t octinv = (negx ? 0u : 4u) | (negy ? 0u : 2u) | (negz ? 0u : 1u);
+    const uint32_t octinv4 = octinv * 0x01010101u;
+
+    uint32_t stack_x[CRT_STACK_ENTRIES], stack_y[CRT_STACK_ENTRIES];
+    int sp = 0;
+    uint32_t ng_x = 0u, ng_y = 0x80000000u;   // node group: (first child index, hits[31:24] | imask[7:0])
+
+    while (true) {
+        uint32_t tg_x, tg_y;                  // primitive group: (first prim index, hits[23:0])
+        if (ng_y & 0xff000000u) {
+            const int bit = hi_bit(ng_y);
+            ng_y &= ~(1u << bit);
+            if (ng_y & 0xff000000u) { stack_x[sp] = ng_x; stack_y[sp] = ng_y; sp++; }
+            const uint32_t slot = (uint32_t)(bit - 24) ^ octinv;
+            const uint32_t rel = (uint32_t)pop_count(ng_y & ((1u << slot) - 1u) & 0xffu);
+            const WideNode* node = sc.nodes + (ng_x + rel);
+            const u4 n0 = ld_u4(&node->n0);
+            const u4 n1 = ld_u4(&node->n1);
+            const u4 n2 = ld_u4(&node->n2);
+            const u4 n3 = ld_u4(&node->n3);
+            const u4 n4 = ld_u4(&node->n4);
+            if (COUNT) ctr->nodes++;
+
+            const float px = bits_f(n0.x), py = bits_f(n0.y), pz = bits_f(n0.z);
+            const uint32_t ew = n0.w;
+            const float sx = bits_f((ew & 0xffu) << 23) * idx;
+            const float sy = bits_f(((ew >> 8) & 0xffu) << 23) * idy;
+            const float sz = bits_f(((ew >> 16) & 0xffu) << 23) * idz;
+            const float ox = (px - o.x) * idx, oy = (py - o.y) * idy, oz = (pz - o.z) * idz;
+            // conservative slack: covers the rounding of (p-o)*idir and of the per-child fma
+            const float eps = 4.76837158203125e-07f;   // 2^-21
+            const float padx = eps * (fabsf(ox) + 256.f * fabsf(sx));
+            const float pady = eps * (fabsf(oy) + 256.f * fabsf(sy));
+            const float padz = eps * (fabsf(oz) + 256.f * fabsf(sz));
+            const float oxn = ox - padx, oxf = ox + padx;
+            const float oyn = oy - pady, oyf = oy + pady;
+            const float ozn = oz - padz, ozf = oz + padz;
+
+            uint32_t hitmask = 0u;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (int half = 0; half < 2; half++) {
+                const uint32_t meta4 = half ? n1.w : n1.z;
+                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                const uint32_t inner_mask4 = ((is_inner4 >> 4) & 0x01010101u) * 0xffu;
+                const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+                const uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
+                const uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
+                const uint32_t nearx = negx ? qhix : qlox, farx = negx ? qlox : qhix;
+                const uint32_t neary = negy ? qhiy : qloy, fary = negy ? qloy : qhiy;
+                const uint32_t nearz = negz ? qhiz : qloz, farz = negz ? qloz : qhiz;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+                for (int j = 0; j < 4; j++) {
+                    const float t0x = byte_f(nearx, j) * sx + oxn, t1x = byte_f(farx, j) * sx + oxf;
+                    const float t0y = byte_f(neary, j) * sy + oyn, t1y = byte_f(fary, j) * sy + oyf;
+                    const float t0z = byte_f(nearz, j) * sz + ozn, t1z = byte_f(farz, j) * sz + ozf;
+                    const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
+                    const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, rec.t));
+                    if (cmin <= cmax) {
+                        const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu;
+                        const uint32_t bi = (bit_index4 >> (8 * j)) & 0xffu;
+                        hitmask |= cb << bi;
+                    }
+                }
+            }
+            ng_x = n1.x;
+            ng_y = (hitmask & 0xff000000u) | (ew >> 24);
+            tg_x = n1.y;
+            tg_y = hitmask & 0x00ffffffu;
+        } else {
+            tg_x = ng_x;
+            tg_y = ng_y;
+            ng_x = 0u;
+            ng_y = 0u;
+        }
+
+        while (tg_y) {
+            const int i = hi_bit(tg_y);
+            tg_y &= ~(1u << i);
+            if (COUNT) ctr->prims++;
+            test_prim(sc.prims, tg_x + (uint32_t)i, o, d, tmin, rec);
+        }
+
+        if ((ng_y & 0xff000000u) == 0u) {
+            if (sp == 0) break;
+            sp--;
+            ng_x = stack_x[sp];
+            ng_y = stack_y[sp];
+        }
+    }
+    return rec.id >= 0;
+}
+
+}  // namespace crt
