@@ -128,7 +128,10 @@ enum {
     CRT_RENDER_ACCUMULATE = 1u << 0, /* add to the float4 accumulation buffer instead of
                                         overwriting it (the reference always overwrites,
                                         src/CUDAKernels.h:164)                          */
-    CRT_RENDER_NO_TONEMAP = 1u << 1  /* skip the RGBA8 pack (multi-GPU ranks != 0)      */
+    CRT_RENDER_NO_TONEMAP = 1u << 1, /* skip the RGBA8 pack (multi-GPU ranks != 0)      */
+    CRT_RENDER_TIME_KERNELS = 1u << 2 /* bracket every kernel launch with CUDA events on the
+                                        launching stream and report per-kernel-class totals in
+                                        crt_stats (extend_ms / shade_ms); off by default       */
 };
 
 typedef struct crt_render_params {
@@ -156,7 +159,14 @@ typedef struct crt_stats {
     /* traversal work counters, filled only by crt_render_counted */
     uint64_t nodes_fetched;
     uint64_t prims_tested;
-    uint64_t reserved[4];
+    /* per-kernel-class device time of the last crt_render, filled with CRT_RENDER_TIME_KERNELS:
+     * wavefront: extend_ms = sum over k_wf_extend launches, shade_ms = k_wf_begin + k_wf_shade;
+     * megakernel: extend_ms = the one k_render_mega launch, shade_ms = 0 */
+    float    extend_ms;
+    float    shade_ms;
+    uint32_t extend_launches;
+    uint32_t shade_launches;
+    uint64_t reserved[2];
 } crt_stats;
 
 typedef struct crt_ctx crt_ctx;

@@ -1,0 +1,338 @@
+"""ctypes binding of libcrt_b200.so — thin Python mirror of include/crt_api.h.
+
+The product is the C-ABI shared library (CUDA kernels for sm_100a + C++ host code); this module
+only loads it and marshals numpy buffers, for the tests and bench.py. It mirrors the reference's
+operator surface for the render path (reference: CudaRayTracer/src/CUDARenderer.cuh:9-60:
+initialize / updateCamera / render / getImageData / getRandState).
+
+There is no Python or CPU fallback: if the library is missing or has no GPU, calls raise.
+The directory name contains a hyphen, so import it with
+    importlib.import_module("raytracer-cuda_b200")
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcrt_b200.so")
+
+CRT_OK = 0
+E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_IO, E_PARSE, E_LIMIT = -1, -2, -3, -4, -5, -6, -7
+MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT = 0, 1, 2, 3
+MODE_WAVEFRONT, MODE_MEGAKERNEL = 0, 1
+RENDER_ACCUMULATE, RENDER_NO_TONEMAP, RENDER_TIME_KERNELS = 1, 2, 4
+REFERENCE_SEED = 1804289383  # glibc rand() first value = what CUDARenderer::initialize passes (CUDARenderer.cuh:46)
+
+
+class Material(C.Structure):
+    _fields_ = [("type", C.c_int32), ("albedo", C.c_float * 3), ("emission", C.c_float * 3),
+                ("roughness", C.c_float), ("ior", C.c_float)]
+
+
+class Scene(C.Structure):
+    _fields_ = [("positions", C.POINTER(C.c_float)), ("num_vertices", C.c_uint32),
+                ("indices", C.POINTER(C.c_uint32)), ("tri_material", C.POINTER(C.c_int32)),
+                ("num_triangles", C.c_uint32),
+                ("spheres", C.POINTER(C.c_float)), ("sphere_material", C.POINTER(C.c_int32)),
+                ("num_spheres", C.c_uint32),
+                ("materials", C.POINTER(Material)), ("num_materials", C.c_uint32),
+                ("mesh_tri_offset", C.POINTER(C.c_uint32)), ("num_meshes", C.c_uint32)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("position", C.c_float * 3), ("world_up", C.c_float * 3), ("yaw_deg", C.c_float),
+                ("pitch_deg", C.c_float), ("vfov_deg", C.c_float), ("aspect", C.c_float),
+                ("aperture", C.c_float), ("focus_dist", C.c_float)]
+
+
+class Config(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("device", C.c_int32), ("mode", C.c_int32),
+                ("bvh_leaf_max", C.c_int32), ("reserved", C.c_int32 * 7)]
+
+
+class RenderParams(C.Structure):
+    _fields_ = [("spp", C.c_int32), ("max_bounces", C.c_int32), ("min_bounces", C.c_int32),
+                ("rr_max_prob", C.c_float), ("flags", C.c_uint32), ("reserved", C.c_int32 * 3)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("rays_total", C.c_uint64), ("samples", C.c_uint64),
+                ("render_ms", C.c_float), ("bvh_build_ms", C.c_float), ("rng_init_ms", C.c_float),
+                ("scene_upload_ms", C.c_float), ("bvh_nodes", C.c_uint32), ("bvh_prims", C.c_uint32),
+                ("bvh_depth", C.c_uint32), ("kernel_launches", C.c_uint32),
+                ("nodes_fetched", C.c_uint64), ("prims_tested", C.c_uint64), ("extend_ms", C.c_float), ("shade_ms", C.c_float),
+                ("extend_launches", C.c_uint32), ("shade_launches", C.c_uint32), ("reserved", C.c_uint64 * 2)]
+
+
+class CrtError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("crt error %d: %s" % (code, message))
+        self.code = code
+
+
+_lib = None
+
+
+def load_library():
+    """Load libcrt_b200.so (built by `make -C raytracer-cuda_b200`). Raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FileNotFoundError("%s not found: build it with __graft_entry__.build() / make -C raytracer-cuda_b200 "
+                                "(there is no Python fallback)" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    P = C.c_void_p
+    sig = {
+        "crt_api_version": (C.c_int, []),
+        "crt_create": (C.c_int, [C.POINTER(P), C.POINTER(Config)]),
+        "crt_destroy": (None, [P]),
+        "crt_last_error": (C.c_char_p, [P]),
+        "crt_init_rng": (C.c_int, [P, C.c_uint64, C.c_uint64]),
+        "crt_set_scene": (C.c_int, [P, C.POINTER(Scene)]),
+        "crt_set_camera": (C.c_int, [P, C.POINTER(Camera)]),
+        "crt_render": (C.c_int, [P, C.POINTER(RenderParams)]),
+        "crt_render_counted": (C.c_int, [P, C.POINTER(RenderParams)]),
+        "crt_primary_ids": (C.c_int, [P, C.c_uint64, C.c_uint64, P, P]),
+        "crt_get_image_rgba8": (C.c_int, [P, P, C.POINTER(P)]),
+        "crt_get_accum": (C.c_int, [P, P, C.POINTER(P)]),
+        "crt_set_accum": (C.c_int, [P, P]),
+        "crt_tonemap": (C.c_int, [P]),
+        "crt_get_rng_state": (C.c_int, [P, P, C.POINTER(P)]),
+        "crt_set_rng_state": (C.c_int, [P, P]),
+        "crt_get_stats": (C.c_int, [P, C.POINTER(Stats)]),
+        "crt_get_stream": (C.c_int, [P, C.POINTER(P)]),
+        "crt_scene_builtin": (C.c_int, [C.c_char_p, C.c_int32, C.POINTER(C.POINTER(Scene)), C.POINTER(Camera)]),
+        "crt_scene_free": (None, [C.POINTER(Scene)]),
+        "crt_scene_load_obj": (C.c_int, [C.POINTER(C.c_char_p), C.c_int32, C.c_int32, C.POINTER(C.POINTER(Scene)),
+                                         C.c_char_p, C.c_size_t]),
+        "crt_write_ppm": (C.c_int, [P, C.c_char_p]),
+        "crt_write_pfm": (C.c_int, [P, C.c_char_p]),
+        "crt_checkpoint_save": (C.c_int, [P, C.c_char_p]),
+        "crt_checkpoint_load": (C.c_int, [P, C.c_char_p]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)   # AttributeError here = the header and the library disagree
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+API_FUNCTIONS = ["crt_api_version", "crt_create", "crt_destroy", "crt_last_error", "crt_init_rng", "crt_set_scene",
+                 "crt_set_camera", "crt_render", "crt_render_counted", "crt_primary_ids", "crt_get_image_rgba8",
+                 "crt_get_accum", "crt_set_accum", "crt_tonemap", "crt_get_rng_state", "crt_set_rng_state",
+                 "crt_get_stats", "crt_get_stream", "crt_scene_builtin", "crt_scene_free", "crt_scene_load_obj",
+                 "crt_write_ppm", "crt_write_pfm", "crt_checkpoint_save", "crt_checkpoint_load"]
+
+
+class SceneHandle:
+    """A library-owned crt_scene (built-in or loaded from OBJ). Keeps numpy views of its arrays."""
+
+    def __init__(self, ptr, camera=None):
+        self._ptr = ptr
+        self.camera = camera
+        s = ptr.contents
+        self.num_triangles, self.num_spheres = s.num_triangles, s.num_spheres
+        self.num_vertices, self.num_materials, self.num_meshes = s.num_vertices, s.num_materials, s.num_meshes
+
+    @property
+    def struct(self):
+        return self._ptr.contents
+
+    def pointer(self):
+        return self._ptr
+
+    def arrays(self):
+        s = self._ptr.contents
+        out = {}
+        out["positions"] = np.ctypeslib.as_array(s.positions, shape=(s.num_vertices, 3)).copy() if s.num_vertices else np.zeros((0, 3), np.float32)
+        out["indices"] = np.ctypeslib.as_array(s.indices, shape=(s.num_triangles, 3)).copy() if s.num_triangles else np.zeros((0, 3), np.uint32)
+        out["tri_material"] = np.ctypeslib.as_array(s.tri_material, shape=(s.num_triangles,)).copy() if s.num_triangles else np.zeros((0,), np.int32)
+        out["spheres"] = np.ctypeslib.as_array(s.spheres, shape=(s.num_spheres, 4)).copy() if s.num_spheres else np.zeros((0, 4), np.float32)
+        out["sphere_material"] = np.ctypeslib.as_array(s.sphere_material, shape=(s.num_spheres,)).copy() if s.num_spheres else np.zeros((0,), np.int32)
+        out["mesh_tri_offset"] = np.ctypeslib.as_array(s.mesh_tri_offset, shape=(s.num_meshes + 1,)).copy() if s.num_meshes else np.zeros((0,), np.uint32)
+        out["materials"] = [(m.type, tuple(m.albedo), tuple(m.emission), m.roughness, m.ior) for m in (s.materials[i] for i in range(s.num_materials))]
+        return out
+
+    def free(self):
+        if self._ptr is not None:
+            load_library().crt_scene_free(self._ptr)
+            self._ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def builtin_scene(name, param=0):
+    """crt_scene_builtin: 'cornell' (C1), 'cornell_blob' (C2/C5), 'spheres' (C3), 'terrain' (C4)."""
+    lib = load_library()
+    ptr = C.POINTER(Scene)()
+    cam = Camera()
+    rc = lib.crt_scene_builtin(name.encode(), int(param), C.byref(ptr), C.byref(cam))
+    if rc != CRT_OK:
+        raise CrtError(rc, "unknown built-in scene %r" % name)
+    return SceneHandle(ptr, cam)
+
+
+def load_obj(paths, add_reference_spheres=True):
+    """crt_scene_load_obj: the reference's SceneManager::loadObject rules (SceneManager.h:198-329)."""
+    lib = load_library()
+    arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
+    ptr = C.POINTER(Scene)()
+    err = C.create_string_buffer(512)
+    rc = lib.crt_scene_load_obj(arr, len(paths), 1 if add_reference_spheres else 0, C.byref(ptr), err, 512)
+    if rc != CRT_OK:
+        raise CrtError(rc, err.value.decode(errors="replace"))
+    return SceneHandle(ptr)
+
+
+def make_scene_struct(positions, indices, tri_material, spheres, sphere_material, materials, mesh_tri_offset=None):
+    """Build a crt_scene from numpy arrays. Returns (Scene, keepalive)."""
+    pos = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
+    idx = np.ascontiguousarray(indices, np.uint32).reshape(-1, 3)
+    tm = np.ascontiguousarray(tri_material, np.int32).reshape(-1)
+    sph = np.ascontiguousarray(spheres, np.float32).reshape(-1, 4)
+    sm = np.ascontiguousarray(sphere_material, np.int32).reshape(-1)
+    mats = (Material * max(len(materials), 1))()
+    for i, (t, alb, emi, rough, ior) in enumerate(materials):
+        mats[i].type = t
+        mats[i].albedo[:] = alb
+        mats[i].emission[:] = emi
+        mats[i].roughness = rough
+        mats[i].ior = ior
+    s = Scene()
+    s.positions = pos.ctypes.data_as(C.POINTER(C.c_float))
+    s.num_vertices = pos.shape[0]
+    s.indices = idx.ctypes.data_as(C.POINTER(C.c_uint32))
+    s.tri_material = tm.ctypes.data_as(C.POINTER(C.c_int32))
+    s.num_triangles = idx.shape[0]
+    s.spheres = sph.ctypes.data_as(C.POINTER(C.c_float))
+    s.sphere_material = sm.ctypes.data_as(C.POINTER(C.c_int32))
+    s.num_spheres = sph.shape[0]
+    s.materials = C.cast(mats, C.POINTER(Material))
+    s.num_materials = len(materials)
+    keep = [pos, idx, tm, sph, sm, mats]
+    if mesh_tri_offset is not None and len(mesh_tri_offset) >= 2:
+        off = np.ascontiguousarray(mesh_tri_offset, np.uint32)
+        s.mesh_tri_offset = off.ctypes.data_as(C.POINTER(C.c_uint32))
+        s.num_meshes = len(off) - 1
+        keep.append(off)
+    return s, keep
+
+
+class Renderer:
+    """CUDARenderer-shaped wrapper of a crt_ctx (reference: src/CUDARenderer.cuh:9-29)."""
+
+    def __init__(self, width, height, device=0, mode=MODE_WAVEFRONT, bvh_leaf_max=0):
+        self.lib = load_library()
+        self.width, self.height = int(width), int(height)
+        cfg = Config(width=self.width, height=self.height, device=device, mode=mode, bvh_leaf_max=bvh_leaf_max)
+        self._ctx = C.c_void_p()
+        rc = self.lib.crt_create(C.byref(self._ctx), C.byref(cfg))
+        if rc != CRT_OK:
+            msg = self.lib.crt_last_error(None).decode(errors="replace")
+            self._ctx = None
+            raise CrtError(rc, msg)
+
+    def _check(self, rc):
+        if rc != CRT_OK:
+            raise CrtError(rc, self.lib.crt_last_error(self._ctx).decode(errors="replace"))
+
+    # CUDARenderer::initialize's initRandState launch
+    def initialize(self, seed=REFERENCE_SEED, subsequence_base=0):
+        self._check(self.lib.crt_init_rng(self._ctx, int(seed), int(subsequence_base)))
+
+    def set_scene(self, scene):
+        ptr = scene.pointer() if isinstance(scene, SceneHandle) else C.pointer(scene)
+        self._check(self.lib.crt_set_scene(self._ctx, ptr))
+
+    # CUDARenderer::updateCamera
+    def update_camera(self, camera):
+        self._check(self.lib.crt_set_camera(self._ctx, C.byref(camera)))
+
+    # CUDARenderer::render
+    def render(self, spp, max_bounces=20, min_bounces=3, rr_max_prob=0.95, flags=0, counted=False):
+        p = RenderParams(spp=int(spp), max_bounces=int(max_bounces), min_bounces=int(min_bounces),
+                         rr_max_prob=float(rr_max_prob), flags=int(flags))
+        fn = self.lib.crt_render_counted if counted else self.lib.crt_render
+        self._check(fn(self._ctx, C.byref(p)))
+        return self.stats()
+
+    def primary_ids(self, seed=REFERENCE_SEED, subsequence_base=0):
+        ids = np.empty((self.height, self.width), np.int32)
+        t = np.empty((self.height, self.width), np.float32)
+        self._check(self.lib.crt_primary_ids(self._ctx, int(seed), int(subsequence_base), ids.ctypes.data, t.ctypes.data))
+        return ids, t
+
+    # CUDARenderer::getImageData (+ the D2H copy of WindowManager::drawFrame); row 0 = bottom
+    def image_rgba8(self, out=None):
+        img = out if out is not None else np.empty((self.height, self.width, 4), np.uint8)
+        self._check(self.lib.crt_get_image_rgba8(self._ctx, img.ctypes.data, None))
+        return img
+
+    def accum(self, out=None):
+        acc = out if out is not None else np.empty((self.height, self.width, 4), np.float32)
+        self._check(self.lib.crt_get_accum(self._ctx, acc.ctypes.data, None))
+        return acc
+
+    def accum_device_ptr(self):
+        p = C.c_void_p()
+        self._check(self.lib.crt_get_accum(self._ctx, None, C.byref(p)))
+        return p.value
+
+    def set_accum(self, acc):
+        a = np.ascontiguousarray(acc, np.float32)
+        assert a.size == self.width * self.height * 4
+        self._check(self.lib.crt_set_accum(self._ctx, a.ctypes.data))
+
+    def tonemap(self):
+        self._check(self.lib.crt_tonemap(self._ctx))
+
+    # CUDARenderer::getRandState as 6 planes (v0..v4, d)
+    def rng_state(self):
+        st = np.empty((6, self.height, self.width), np.uint32)
+        self._check(self.lib.crt_get_rng_state(self._ctx, st.ctypes.data, None))
+        return st
+
+    def set_rng_state(self, st):
+        a = np.ascontiguousarray(st, np.uint32)
+        assert a.size == self.width * self.height * 6
+        self._check(self.lib.crt_set_rng_state(self._ctx, a.ctypes.data))
+
+    def stats(self):
+        s = Stats()
+        self._check(self.lib.crt_get_stats(self._ctx, C.byref(s)))
+        return s
+
+    def stream(self):
+        p = C.c_void_p()
+        self._check(self.lib.crt_get_stream(self._ctx, C.byref(p)))
+        return p.value
+
+    def write_ppm(self, path):
+        self._check(self.lib.crt_write_ppm(self._ctx, path.encode()))
+
+    def write_pfm(self, path):
+        self._check(self.lib.crt_write_pfm(self._ctx, path.encode()))
+
+    def checkpoint_save(self, path):
+        self._check(self.lib.crt_checkpoint_save(self._ctx, path.encode()))
+
+    def checkpoint_load(self, path):
+        self._check(self.lib.crt_checkpoint_load(self._ctx, path.encode()))
+
+    def close(self):
+        if self._ctx is not None and self._ctx.value:
+            self.lib.crt_destroy(self._ctx)
+        self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

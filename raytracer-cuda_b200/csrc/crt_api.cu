@@ -239,8 +239,9 @@ static int render_impl(crt_ctx* ctx, const crt_render_params* p, bool counted) {
     CU(cudaMemsetAsync(ctx->fb.counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
     uint32_t launches = 0;
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    KernelTimes kt;
     if (ctx->cfg.mode == CRT_MODE_MEGAKERNEL) CU(launch_render_mega(a, counted, ctx->num_sms, ctx->stream, &launches));
-    else CU(launch_render_wavefront(ctx->wf, a, counted, ctx->num_sms, ctx->stream, &launches));
+    else CU(launch_render_wavefront(ctx->wf, a, counted, ctx->num_sms, ctx->stream, &launches, &kt));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     unsigned long long c[4] = {0, 0, 0, 0};
     CU(cudaMemcpyAsync(c, ctx->fb.counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
@@ -252,6 +253,9 @@ static int render_impl(crt_ctx* ctx, const crt_render_params* p, bool counted) {
     ctx->stats.nodes_fetched = c[2];
     ctx->stats.prims_tested = c[3];
     ctx->stats.kernel_launches = launches;
+    if (ctx->cfg.mode == CRT_MODE_MEGAKERNEL) { kt.extend_ms = ctx->stats.render_ms; kt.extend_launches = 1; }
+    ctx->stats.extend_ms = kt.extend_ms; ctx->stats.shade_ms = kt.shade_ms;
+    ctx->stats.extend_launches = kt.extend_launches; ctx->stats.shade_launches = kt.shade_launches;
     return CRT_OK;
 }
 

@@ -25,6 +25,11 @@ struct RenderArgs {
     uint32_t flags;       // CRT_RENDER_*
 };
 
+struct KernelTimes {
+    float extend_ms = 0.f, shade_ms = 0.f;
+    uint32_t extend_launches = 0, shade_launches = 0;
+};
+
 // crt_render.cu — every launcher enqueues on `stream` and returns the launch error (no sync).
 cudaError_t launch_rng_init(uint32_t* rng_planes, int width, int height, unsigned long long seed,
                             unsigned long long subseq_base, int num_sms, cudaStream_t stream);
@@ -38,6 +43,6 @@ struct WavefrontState;   // persistent path state, owned by the context
 cudaError_t wavefront_create(WavefrontState** out, int width, int height);
 void wavefront_destroy(WavefrontState* s);
 cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, bool counted, int num_sms, cudaStream_t stream,
-                                    uint32_t* launches);
+                                    uint32_t* launches, KernelTimes* times);
 
 }  // namespace crt

@@ -31,6 +31,7 @@ struct WavefrontState {
     uint32_t* h_qcount = nullptr;   // pinned
     size_t n = 0;
     int blocks_extend = 0, blocks_shade = 0;
+    cudaEvent_t ev[3 * 16 + 2] = {};   // CRT_RENDER_TIME_KERNELS: begin pair + 3 events per iteration of a batch
 };
 
 struct WfView {
@@ -221,28 +222,40 @@ void wavefront_destroy(WavefrontState* s) {
     if (!s) return;
     cudaFree(s->A); cudaFree(s->B); cudaFree(s->C); cudaFree(s->queue[0]); cudaFree(s->queue[1]); cudaFree(s->qcount);
     if (s->h_qcount) cudaFreeHost(s->h_qcount);
+    for (cudaEvent_t ev : s->ev) if (ev) cudaEventDestroy(ev);
     delete s;
 }
 
 cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, bool counted, int num_sms, cudaStream_t stream,
-                                    uint32_t* launches) {
+                                    uint32_t* launches, KernelTimes* times) {
     if (!ws) return cudaErrorInvalidValue;
     WfView w;
     w.A = ws->A; w.B = ws->B; w.C = ws->C;
     const int grid_e = num_sms * ws->blocks_extend, grid_s = num_sms * ws->blocks_shade;
+    const int batch = 16;
+    const bool timed = times != nullptr && (a.flags & CRT_RENDER_TIME_KERNELS);
+    cudaError_t e = cudaSuccess;
+    if (timed && !ws->ev[0])
+        for (int i = 0; i < 3 * batch + 2 && e == cudaSuccess; i++) e = cudaEventCreate(&ws->ev[i]);
+    if (e != cudaSuccess) return e;
     uint32_t nl = 0;
+    if (timed) cudaEventRecord(ws->ev[3 * batch], stream);
     k_wf_begin<<<grid_s, 256, 0, stream>>>(a, w, ws->queue[0], ws->qcount);
+    if (timed) cudaEventRecord(ws->ev[3 * batch + 1], stream);
     nl++;
     int cur = 0;
     const long long max_iters = (long long)a.rc.spp * a.rc.max_bounces + 1;
-    const int batch = 16;
     long long it = 0;
-    cudaError_t e = cudaGetLastError();
+    bool first = true;
+    e = cudaGetLastError();
     while (e == cudaSuccess && it < max_iters) {
         for (int b = 0; b < batch; b++) {
+            if (timed) cudaEventRecord(ws->ev[3 * b], stream);
             if (counted) k_wf_extend<true><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters);
             else k_wf_extend<false><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters);
+            if (timed) cudaEventRecord(ws->ev[3 * b + 1], stream);
             k_wf_shade<<<grid_s, 256, 0, stream>>>(a, w, ws->queue[cur], ws->queue[cur ^ 1], ws->qcount, cur);
+            if (timed) cudaEventRecord(ws->ev[3 * b + 2], stream);
             nl += 2;
             cur ^= 1;
             it++;
@@ -251,6 +264,16 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         if (e != cudaSuccess) break;
         e = cudaMemcpyAsync(ws->h_qcount, ws->qcount, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+        if (e == cudaSuccess && timed) {
+            float ms = 0.f;
+            if (first) { cudaEventElapsedTime(&ms, ws->ev[3 * batch], ws->ev[3 * batch + 1]); times->shade_ms += ms; times->shade_launches++; first = false; }
+            for (int b = 0; b < batch; b++) {
+                cudaEventElapsedTime(&ms, ws->ev[3 * b], ws->ev[3 * b + 1]); times->extend_ms += ms;
+                cudaEventElapsedTime(&ms, ws->ev[3 * b + 1], ws->ev[3 * b + 2]); times->shade_ms += ms;
+            }
+            times->extend_launches += batch;
+            times->shade_launches += batch;
+        }
         if (e == cudaSuccess && ws->h_qcount[cur] == 0u) break;
     }
     if (launches) *launches += nl;
