@@ -183,8 +183,9 @@ float evaluate_sah(const Mesh& m, int axis, float pos, int start, int end) {   /
         if (comp(c, axis) < pos) { lc++; expand_tri(m, lb, i); }
         else { rc++; expand_tri(m, rb, i); }
     }
-    // leftCount * leftBox.area() + rightCount * rightBox.area()  -> fma(lc, la, rc*ra)
-    float cost = fmaf((float)lc, box_area(lb), (float)rc * box_area(rb));
+    // leftCount * leftBox.area() + rightCount * rightBox.area(): the reference's SASS (initMesh, sm_100)
+    // is FMUL(la, lc) then FFMA(ra, rc, .)  -> fma(rc, ra, lc*la); pinned by tests/golden/c2s_perm_i32.bin
+    float cost = fmaf((float)rc, box_area(rb), (float)lc * box_area(lb));
     return cost < 1e-8f ? 1e-8f : cost;
 }
 

@@ -54,8 +54,9 @@ static inline V3 reflect(V3 v, V3 n) {
     float k = d + d;
     return V3{fmaf(-n.x, k, v.x), fmaf(-n.y, k, v.y), fmaf(-n.z, k, v.z)};
 }
-// dot(-u, n) as the reference evaluates it inside Dielectric::scatter / refract
-static inline float dot_neg(V3 u, V3 n) { return fmaf(-u.z, n.z, fmaf(-u.x, n.x, (-u.y) * n.y)); }
+// dot(-u, n) as the reference evaluates it inside Dielectric::scatter / refract. SASS of the sm_100 build:
+// FMUL t = u.x*n.x; FFMA t = -u.y*n.y - t; FFMA -u.z*n.z + t   (x is the plain multiply here, unlike dot())
+static inline float dot_neg(V3 u, V3 n) { return fmaf(-u.z, n.z, fmaf(-u.y, n.y, -(u.x * n.x))); }
 // reference: Vec3.cuh:228-233
 static inline V3 refract(V3 uv, V3 n, float eta) {
     float cos_theta = fminf(dot_neg(uv, n), 1.0f);

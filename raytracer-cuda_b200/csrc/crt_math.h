@@ -76,8 +76,9 @@ CRT_HD vec3 v_reflect(vec3 v, vec3 n) {
     float k = f_add(d, d);
     return mk3(f_fma(-n.x, k, v.x), f_fma(-n.y, k, v.y), f_fma(-n.z, k, v.z));
 }
-// dot(-u, n) as compiled inside Dielectric::scatter / refract
-CRT_HD float v_dot_neg(vec3 u, vec3 n) { return f_fma(-u.z, n.z, f_fma(-u.x, n.x, f_mul(-u.y, n.y))); }
+// dot(-u, n) as compiled inside Dielectric::scatter / refract: the reference's SASS multiplies the x
+// terms plainly and fuses y then z (FMUL x*nx; FFMA -y*ny - t; FFMA -z*nz + t)
+CRT_HD float v_dot_neg(vec3 u, vec3 n) { return f_fma(-u.z, n.z, f_fma(-u.y, n.y, -f_mul(u.x, n.x))); }
 // refract(uv, n, eta)                                                   (Vec3.cuh:228-233)
 CRT_HD vec3 v_refract(vec3 uv, vec3 n, float eta) {
     float c = fminf(v_dot_neg(uv, n), 1.0f);
