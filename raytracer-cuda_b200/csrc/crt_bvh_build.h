@@ -228,6 +228,7 @@ struct PlocCompactFn {
 
 
 // ---- step 4: collapse to the 8-wide compressed layout ---------------------------------------
+CRT_HD float box_max_extent(const f4& lo, const f4& hi) { return fmaxf(hi.x - lo.x, fmaxf(hi.y - lo.y, hi.z - lo.z)); }
 CRT_HD float box_half_area(const f4& lo, const f4& hi) {
     const float ex = hi.x - lo.x, ey = hi.y - lo.y, ez = hi.z - lo.z;
     return ex * ey + ey * ez + ez * ex;
@@ -286,7 +287,17 @@ struct CollapseFn {
         const uint32_t b = wide_bnode[w];
         uint32_t ch[8];
         int nch;
-        if (bcount[b] <= leaf_max) {          // tiny scene: the root itself is one leaf
+        // node frame
+        const f4 nlo = blo[b], nhi = bhi[b];
+        // Child boxes are stored on this node's 8-bit grid (step = extent/255 per axis). A subtree that is
+        // tiny next to the frame (the Cornell box beside the reference's r=999 ground sphere,
+        // CUDAKernels.h:69) would be inflated to a whole grid cell and hit by every ray, so such a
+        // subtree is neither opened into this node nor stored as a leaf slot: it stays an inner child
+        // and gets a wide node with its own tight frame.
+        const float frame = fmax3(nhi.x - nlo.x, nhi.y - nlo.y, nhi.z - nlo.z);
+        const float open_min = frame * (1.0f / 16.0f);     // open a child only if it spans >= 16 grid steps
+        const float leaf_min = frame * (1.0f / 64.0f);     // leaf slot only if it spans >= 4 grid steps
+        if (bcount[b] <= leaf_max) {          // a subtree of <= leaf_max primitives: one leaf slot
             ch[0] = b;
             nch = 1;
         } else {
@@ -298,6 +309,7 @@ struct CollapseFn {
                 float best_area = -1.f;
                 for (int i = 0; i < nch; i++) {
                     if (bcount[ch[i]] <= leaf_max) continue;
+                    if (box_max_extent(blo[ch[i]], bhi[ch[i]]) < open_min) continue;
                     const float a = box_half_area(blo[ch[i]], bhi[ch[i]]);
                     if (a > best_area) { best_area = a; best = i; }
                 }
@@ -307,8 +319,10 @@ struct CollapseFn {
                 ch[nch++] = right_of(c);
             }
         }
-        // node frame
-        const f4 nlo = blo[b], nhi = bhi[b];
+        // leaf slot or inner child?
+        bool as_leaf[8];
+        for (int i = 0; i < nch; i++)
+            as_leaf[i] = bcount[ch[i]] <= leaf_max && (nch == 1 || box_max_extent(blo[ch[i]], bhi[ch[i]]) >= leaf_min);
         const uint32_t ex = quant_exponent(nhi.x - nlo.x), ey = quant_exponent(nhi.y - nlo.y), ez = quant_exponent(nhi.z - nlo.z);
         const double scx = ex ? ldexp(1.0, (int)ex - 127) : 0.0, scy = ey ? ldexp(1.0, (int)ey - 127) : 0.0, scz = ez ? ldexp(1.0, (int)ez - 127) : 0.0;
         const float ncx = 0.5f * (nlo.x + nhi.x), ncy = 0.5f * (nlo.y + nhi.y), ncz = 0.5f * (nlo.z + nhi.z);
@@ -345,7 +359,7 @@ struct CollapseFn {
         // allocate children
         uint32_t n_inner = 0, n_prims = 0;
         for (int i = 0; i < nch; i++) {
-            if (bcount[ch[i]] <= leaf_max) n_prims += bcount[ch[i]];
+            if (as_leaf[i]) n_prims += bcount[ch[i]];
             else n_inner++;
         }
         const uint32_t child_base = n_inner ? atomic_add_u32(&counters[0], n_inner) : 0u;
@@ -370,7 +384,7 @@ struct CollapseFn {
             v = scx > 0.0 ? ceil(((double)hi.x - (double)nlo.x) / scx) : 0.0; qhx[s] = (uint32_t)(v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v));
             v = scy > 0.0 ? ceil(((double)hi.y - (double)nlo.y) / scy) : 0.0; qhy[s] = (uint32_t)(v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v));
             v = scz > 0.0 ? ceil(((double)hi.z - (double)nlo.z) / scz) : 0.0; qhz[s] = (uint32_t)(v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v));
-            if (bcount[c] > leaf_max) {
+            if (!as_leaf[i]) {
                 imask |= 1u << s;
                 meta[s] = (1u << 5) | (24u + (uint32_t)s);
                 wide_bnode[child_base + inner_rank] = c;

@@ -109,8 +109,9 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
     uint32_t root = 0;
     ex.download(&root, cl_in, sizeof(uint32_t));
 
-    // 4. collapse. At most N-1 inner binary nodes -> at most max(N-1,1) wide nodes; N prim records.
-    const uint32_t node_cap = N > 1 ? N - 1 : 1;
+    // 4. collapse. Every wide node stands for a distinct binary node (an inner one, or a small subtree that
+    // was given its own frame, CollapseFn), of which there are 2N-1; N prim records.
+    const uint32_t node_cap = 2 * N;
     out.nodes = ex.template alloc<WideNode>(node_cap);
     out.prims = ex.template alloc<PrimRec>(N);
     uint32_t* wide_bnode = ex.template alloc<uint32_t>(node_cap);

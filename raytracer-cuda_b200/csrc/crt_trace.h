@@ -127,6 +127,9 @@ CRT_HD bool trace_closest(const SceneView& sc, vec3 o, vec3 d, float tmin, float
             const u4 n3 = ld_u4(&node->n3);
             const u4 n4 = ld_u4(&node->n4);
             if (COUNT) ctr->nodes++;
+#ifdef CRT_NODE_HOOK
+            CRT_NODE_HOOK(ng_x + rel);
+#endif
 
             const float px = bits_f(n0.x), py = bits_f(n0.y), pz = bits_f(n0.z);
             const uint32_t ew = n0.w;
@@ -189,6 +192,9 @@ CRT_HD bool trace_closest(const SceneView& sc, vec3 o, vec3 d, float tmin, float
             const int i = hi_bit(tg_y);
             tg_y &= ~(1u << i);
             if (COUNT) ctr->prims++;
+#ifdef CRT_PRIM_HOOK
+            CRT_PRIM_HOOK(tg_x + (uint32_t)i);
+#endif
             test_prim(sc.prims, tg_x + (uint32_t)i, o, d, tmin, rec);
         }
 
