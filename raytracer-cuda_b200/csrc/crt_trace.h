@@ -91,33 +91,56 @@ CRT_HD bool test_prim(const PrimRec* prims, uint32_t index, vec3 o, vec3 d, floa
     return true;
 }
 
-// Closest hit in [tmin, tmax]. COUNT switches the work counters on (crt_render_counted).
-template <bool COUNT>
-CRT_HD bool trace_closest(const SceneView& sc, vec3 o, vec3 d, float tmin, float tmax, HitRec& rec, TraceCounters* ctr) {
-    rec.t = tmax;
-    rec.prim = 0u;
-    rec.id = -1;
+// ---- resumable traversal ---------------------------------------------------------------------------
+// The closest-hit query as a state machine, so that a warp can interleave lanes that are at
+// different points of their traversals and replace a finished ray at once (persistent threads with
+// dynamic fetch, crt_wavefront.cu) instead of idling until the warp's longest ray is done.
+//   begin(o, d, tmin, tmax)  set up a ray
+//   step<COUNT>(sc, ctr)     one wide-node visit (8 child boxes) plus the primitive tests it produced;
+//                            returns true when the traversal is finished (rec holds the result)
+// Entries of the traversal stack are either node groups (hit bits in [31:24]) or primitive groups
+// (bits [23:0]); a primitive group that only few lanes of the warp hold is postponed to the stack so
+// that the lanes of a warp run the primitive tests together (after Ylitie, Karras, Laine 2017, sec. 4).
+#ifndef CRT_POSTPONE_LANES
+#define CRT_POSTPONE_LANES 6
+#endif
 
-    // reciprocal direction with zero components nudged (box tests only; primitive tests use d)
-    const float tiny = 1e-20f;
-    const float ddx = fabsf(d.x) < tiny ? (d.x < 0.f ? -tiny : tiny) : d.x;
-    const float ddy = fabsf(d.y) < tiny ? (d.y < 0.f ? -tiny : tiny) : d.y;
-    const float ddz = fabsf(d.z) < tiny ? (d.z < 0.f ? -tiny : tiny) : d.z;
-    const float idx = 1.0f / ddx, idy = 1.0f / ddy, idz = 1.0f / ddz;
-    const bool negx = ddx < 0.f, negy = ddy < 0.f, negz = ddz < 0.f;
-    const uint32_t octinv = (negx ? 0u : 4u) | (negy ? 0u : 2u) | (negz ? 0u : 1u);
-    const uint32_t octinv4 = octinv * 0x01010101u;
+struct TravStack {   // kept apart from Traverser so that the scalar state stays in registers
+    uint32_t x[CRT_STACK_ENTRIES], y[CRT_STACK_ENTRIES];
+};
 
-    uint32_t stack_x[CRT_STACK_ENTRIES], stack_y[CRT_STACK_ENTRIES];
-    int sp = 0;
-    uint32_t ng_x = 0u, ng_y = 0x80000000u;   // node group: (first child index, hits[31:24] | imask[7:0])
+struct Traverser {
+    vec3 o, d;
+    float idx, idy, idz;
+    float tmin;
+    HitRec rec;
+    uint32_t ng_x, ng_y;   // node group: (first child index, hits[31:24] | imask[7:0])
+    uint32_t octinv;
+    int sp;
 
-    while (true) {
+    CRT_HD void begin(vec3 o_, vec3 d_, float tmin_, float tmax_) {
+        o = o_; d = d_; tmin = tmin_;
+        rec.t = tmax_; rec.prim = 0u; rec.id = -1;
+        // reciprocal direction with zero components nudged (box tests only; primitive tests use d)
+        const float tiny = 1e-20f;
+        const float ddx = fabsf(d.x) < tiny ? (d.x < 0.f ? -tiny : tiny) : d.x;
+        const float ddy = fabsf(d.y) < tiny ? (d.y < 0.f ? -tiny : tiny) : d.y;
+        const float ddz = fabsf(d.z) < tiny ? (d.z < 0.f ? -tiny : tiny) : d.z;
+        idx = 1.0f / ddx; idy = 1.0f / ddy; idz = 1.0f / ddz;
+        octinv = (ddx < 0.f ? 0u : 4u) | (ddy < 0.f ? 0u : 2u) | (ddz < 0.f ? 0u : 1u);
+        sp = 0;
+        ng_x = 0u; ng_y = 0x80000000u;
+    }
+
+    template <bool COUNT>
+    CRT_HD bool step(const SceneView& sc, TravStack& st, TraceCounters* ctr, int postpone_lanes = CRT_POSTPONE_LANES) {
+        const bool negx = idx < 0.f, negy = idy < 0.f, negz = idz < 0.f;
+        const uint32_t octinv4 = octinv * 0x01010101u;
         uint32_t tg_x, tg_y;                  // primitive group: (first prim index, hits[23:0])
         if (ng_y & 0xff000000u) {
             const int bit = hi_bit(ng_y);
             ng_y &= ~(1u << bit);
-            if (ng_y & 0xff000000u) { stack_x[sp] = ng_x; stack_y[sp] = ng_y; sp++; }
+            if (ng_y & 0xff000000u) { st.x[sp] = ng_x; st.y[sp] = ng_y; sp++; }
             const uint32_t slot = (uint32_t)(bit - 24) ^ octinv;
             const uint32_t rel = (uint32_t)pop_count(ng_y & ((1u << slot) - 1u) & 0xffu);
             const WideNode* node = sc.nodes + (ng_x + rel);
@@ -130,7 +153,6 @@ CRT_HD bool trace_closest(const SceneView& sc, vec3 o, vec3 d, float tmin, float
 #ifdef CRT_NODE_HOOK
             CRT_NODE_HOOK(ng_x + rel);
 #endif
-
             const float px = bits_f(n0.x), py = bits_f(n0.y), pz = bits_f(n0.z);
             const uint32_t ew = n0.w;
             const float sx = bits_f((ew & 0xffu) << 23) * idx;
@@ -189,6 +211,13 @@ CRT_HD bool trace_closest(const SceneView& sc, vec3 o, vec3 d, float tmin, float
         }
 
         while (tg_y) {
+#if defined(__CUDA_ARCH__)
+            // few lanes hold primitives and this lane still has nodes to visit: keep the group for later
+            if ((ng_y & 0xff000000u) && __popc(__activemask()) < postpone_lanes) {
+                st.x[sp] = tg_x; st.y[sp] = tg_y; sp++;
+                break;
+            }
+#endif
             const int i = hi_bit(tg_y);
             tg_y &= ~(1u << i);
             if (COUNT) ctr->prims++;
@@ -199,12 +228,23 @@ CRT_HD bool trace_closest(const SceneView& sc, vec3 o, vec3 d, float tmin, float
         }
 
         if ((ng_y & 0xff000000u) == 0u) {
-            if (sp == 0) break;
+            if (sp == 0) return true;
             sp--;
-            ng_x = stack_x[sp];
-            ng_y = stack_y[sp];
+            ng_x = st.x[sp];
+            ng_y = st.y[sp];
         }
+        return false;
     }
+};
+
+// Closest hit in [tmin, tmax]. COUNT switches the work counters on (crt_render_counted).
+template <bool COUNT>
+CRT_HD bool trace_closest(const SceneView& sc, vec3 o, vec3 d, float tmin, float tmax, HitRec& rec, TraceCounters* ctr) {
+    Traverser tr;
+    TravStack st;
+    tr.begin(o, d, tmin, tmax);
+    while (!tr.step<COUNT>(sc, st, ctr)) {}
+    rec = tr.rec;
     return rec.id >= 0;
 }
 

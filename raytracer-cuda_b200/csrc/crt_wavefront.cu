@@ -16,11 +16,16 @@
 //   A = (o.x, o.y, o.z, thr.x)   B = (d.x, d.y, d.z, thr.y)   C = (t, prim, thr.z, book)
 //   book = sample index (bits 0-23) | bounce (bits 24-31)
 #include <cuda_runtime.h>
+#include <cstdlib>
 
 #include "crt_internal.h"
 #include "crt_shade.h"
 
 namespace crt {
+
+#ifndef CRT_FETCH_LANES
+#define CRT_FETCH_LANES 8
+#endif
 
 struct WavefrontState {
     float4* A = nullptr;
@@ -31,6 +36,7 @@ struct WavefrontState {
     uint32_t* h_qcount = nullptr;   // pinned
     size_t n = 0;
     int blocks_extend = 0, blocks_shade = 0;
+    int fetch_lanes = CRT_FETCH_LANES, postpone_lanes = CRT_POSTPONE_LANES;   // tuning knobs (env CRT_FETCH_LANES / CRT_POSTPONE_LANES)
     cudaEvent_t ev[3 * 16 + 2] = {};   // CRT_RENDER_TIME_KERNELS: begin pair + 3 events per iteration of a batch
 };
 
@@ -82,29 +88,56 @@ __global__ void __launch_bounds__(256) k_wf_begin(RenderArgs a, WfView w, uint32
             queue[i] = (uint32_t)i;
         }
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) { qcount[0] = (uint32_t)n; qcount[1] = 0u; }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { qcount[0] = (uint32_t)n; qcount[1] = 0u; qcount[2] = 0u; }
 }
 
 // ---- extend: closest hit for every queued ray -------------------------------------------------------
+// Persistent warps with dynamic fetch: a warp keeps up to 32 rays in flight and all its lanes advance
+// their traversals one wide node at a time; when CRT_FETCH_LANES lanes have finished, they take the next
+// rays from the queue together (one atomic per refill), so a long ray (one that wanders through the mesh)
+// does not hold 31 finished lanes idle. qcount[2] is the shared fetch cursor (reset by begin / shade).
 template <bool COUNT>
 __global__ void __launch_bounds__(256) k_wf_extend(SceneView scene, WfView w, const uint32_t* queue, uint32_t* qcount, int cur,
-                                                   unsigned long long* counters) {
+                                                   unsigned long long* counters, int fetch_lanes, int postpone_lanes) {
     const uint32_t count = qcount[cur];
-    unsigned long long nodes = 0, prims = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        const uint32_t pix = queue[i];
-        const float4 A = w.A[pix], B = w.B[pix];
-        HitRec h;
-        TraceCounters ctr;
-        ctr.nodes = 0; ctr.prims = 0;
-        const bool hit = trace_closest<COUNT>(scene, mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), 0.001f, INFINITY, h, &ctr);
-        float2* c = reinterpret_cast<float2*>(&w.C[pix]);
-        *c = make_float2(hit ? h.t : -1.f, __uint_as_float(h.prim));
-        if (COUNT) { nodes += ctr.nodes; prims += ctr.prims; }
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    TraceCounters ctr;
+    ctr.nodes = 0; ctr.prims = 0;
+    Traverser tr;
+    TravStack st;
+    bool has_ray = false, exhausted = false;
+    uint32_t pix = 0;
+    while (true) {
+        unsigned idle = __ballot_sync(0xffffffffu, !has_ray);
+        if (!exhausted && __popc(idle) >= fetch_lanes) {
+            const int n = __popc(idle), leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if (lane == leader) base = atomicAdd(&qcount[2], (uint32_t)n);
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (base + (uint32_t)n >= count) exhausted = true;
+            const uint32_t i = base + (uint32_t)__popc(idle & lt_mask);
+            if (!has_ray && i < count) {
+                pix = queue[i];
+                const float4 A = w.A[pix], B = w.B[pix];
+                tr.begin(mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), 0.001f, INFINITY);
+                has_ray = true;
+            }
+            idle = __ballot_sync(0xffffffffu, !has_ray);
+        }
+        if (idle == 0xffffffffu) break;
+        if (has_ray) {
+            if (tr.step<COUNT>(scene, st, &ctr, postpone_lanes)) {
+                float2* c = reinterpret_cast<float2*>(&w.C[pix]);
+                *c = make_float2(tr.rec.id >= 0 ? tr.rec.t : -1.f, __uint_as_float(tr.rec.prim));
+                has_ray = false;
+            }
+        }
     }
     if (COUNT) {
+        unsigned long long nodes = ctr.nodes, prims = ctr.prims;
         for (int o = 16; o > 0; o >>= 1) { nodes += __shfl_xor_sync(0xffffffffu, nodes, o); prims += __shfl_xor_sync(0xffffffffu, prims, o); }
-        if ((threadIdx.x & 31) == 0 && (nodes | prims)) { atomicAdd(&counters[2], nodes); atomicAdd(&counters[3], prims); }
+        if (lane == 0 && (nodes | prims)) { atomicAdd(&counters[2], nodes); atomicAdd(&counters[3], prims); }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         counters[0] += count;        // one ray per queued path; only this thread writes counters[0]
@@ -196,6 +229,7 @@ __global__ void __launch_bounds__(256) k_wf_shade(RenderArgs a, WfView w, const 
         }
         queue_push(queue_out, &qcount[cur ^ 1], keep, pix);
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0) qcount[2] = 0u;   // fetch cursor of the next extend
 }
 
 cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
@@ -211,6 +245,11 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
     int be = 0, bs = 0;
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&be, k_wf_extend<false>, 256, 0);
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade, 256, 0);
+    if (const char* v = getenv("CRT_FETCH_LANES")) s->fetch_lanes = atoi(v);
+    if (const char* v = getenv("CRT_POSTPONE_LANES")) s->postpone_lanes = atoi(v);
+    if (s->fetch_lanes < 1) s->fetch_lanes = 1;
+    if (s->fetch_lanes > 32) s->fetch_lanes = 32;
+    if (const char* v = getenv("CRT_EXTEND_BLOCKS")) be = atoi(v);
     s->blocks_extend = be > 0 ? be : 4;
     s->blocks_shade = bs > 0 ? bs : 4;
     if (e != cudaSuccess) { wavefront_destroy(s); return e; }
@@ -251,8 +290,8 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
     while (e == cudaSuccess && it < max_iters) {
         for (int b = 0; b < batch; b++) {
             if (timed) cudaEventRecord(ws->ev[3 * b], stream);
-            if (counted) k_wf_extend<true><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters);
-            else k_wf_extend<false><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters);
+            if (counted) k_wf_extend<true><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
+            else k_wf_extend<false><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
             if (timed) cudaEventRecord(ws->ev[3 * b + 1], stream);
             k_wf_shade<<<grid_s, 256, 0, stream>>>(a, w, ws->queue[cur], ws->queue[cur ^ 1], ws->qcount, cur);
             if (timed) cudaEventRecord(ws->ev[3 * b + 2], stream);
