@@ -45,12 +45,12 @@ CRT_HD u4 ld_u4(const u4* p) { return *p; }
 
 CRT_HD float byte_f(uint32_t w, int i) { return (float)((w >> (8 * i)) & 0xffu); }
 
-// Primitive test. Returns true when `rec` accepts the hit and updates rec / closest.
-CRT_HD bool test_prim(const PrimRec* prims, uint32_t index, vec3 o, vec3 d, float tmin, HitRec& rec) {
+// Primitive test against the interval [tmin, tmax] (both inclusive, Mesh.cuh:293 / Interval.cuh:33-35).
+// Returns the hit parameter and the caller's primitive id; no tie rule here.
+CRT_HD bool prim_hit(const PrimRec* prims, uint32_t index, vec3 o, vec3 d, float tmin, float tmax, float& t_out, int32_t& id_out) {
     const f4 q0 = ld_f4(&prims[index].q0);
     const f4 q1 = ld_f4(&prims[index].q1);
     const f4 q2 = ld_f4(&prims[index].q2);
-    const int32_t id = (int32_t)f_bits(q2.y);
     float t;
     if (f_bits(q2.w) == (uint32_t)PRIM_TRIANGLE) {
         // Mesh::rayTriangleIntersect, Mesh.cuh:266-293
@@ -68,7 +68,7 @@ CRT_HD bool test_prim(const PrimRec* prims, uint32_t index, vec3 o, vec3 d, floa
         const float v = f_mul(f, v_dot(d, q));
         if (v < 0.f || f_add(u, v) > 1.f) return false;
         t = f_mul(f, v_dot(e2, q));
-        if (t < tmin || t > rec.t) return false;
+        if (t < tmin || t > tmax) return false;
     } else {
         // Sphere::hit, Sphere.cuh:18-34
         const vec3 oc = v_sub(o, mk3(q0.x, q0.y, q0.z));
@@ -79,16 +79,99 @@ CRT_HD bool test_prim(const PrimRec* prims, uint32_t index, vec3 o, vec3 d, floa
         if (disc < 0.f) return false;
         const float sq = f_sqrt(disc);
         t = f_div(f_sub(-half_b, sq), a);
-        if (t < tmin || t > rec.t) {
+        if (t < tmin || t > tmax) {
             t = f_div(f_sub(sq, half_b), a);
-            if (t < tmin || t > rec.t) return false;
+            if (t < tmin || t > tmax) return false;
         }
     }
+    t_out = t;
+    id_out = (int32_t)f_bits(q2.y);
+    return true;
+}
+
+// Sequential form: returns true when `rec` accepts the hit and updates rec.
+CRT_HD bool test_prim(const PrimRec* prims, uint32_t index, vec3 o, vec3 d, float tmin, HitRec& rec) {
+    float t;
+    int32_t id;
+    if (!prim_hit(prims, index, o, d, tmin, rec.t, t, id)) return false;
     if (t == rec.t && id < rec.id) return false;   // order-independent tie rule
     rec.t = t;
     rec.prim = index;
     rec.id = id;
     return true;
+}
+
+// One wide-node visit: the 8 quantised child boxes against the ray interval [tmin, tmax].
+// Out: ng = node group (first child index, hit bits [31:24] | inner mask [7:0]),
+//      tg = primitive group (first primitive index, hit bits [23:0]). Hit bits are ordered so that the
+//      highest bit is the child the ray enters first (octant order).
+CRT_HD void visit_node(const WideNode* node, vec3 o, float idx, float idy, float idz, float tmin, float tmax, uint32_t octinv,
+                       uint32_t& ng_x, uint32_t& ng_y, uint32_t& tg_x, uint32_t& tg_y) {
+    const bool negx = idx < 0.f, negy = idy < 0.f, negz = idz < 0.f;
+    const uint32_t octinv4 = octinv * 0x01010101u;
+    const u4 n0 = ld_u4(&node->n0);
+    const u4 n1 = ld_u4(&node->n1);
+    const u4 n2 = ld_u4(&node->n2);
+    const u4 n3 = ld_u4(&node->n3);
+    const u4 n4 = ld_u4(&node->n4);
+    const float px = bits_f(n0.x), py = bits_f(n0.y), pz = bits_f(n0.z);
+    const uint32_t ew = n0.w;
+    const float sx = bits_f((ew & 0xffu) << 23) * idx;
+    const float sy = bits_f(((ew >> 8) & 0xffu) << 23) * idy;
+    const float sz = bits_f(((ew >> 16) & 0xffu) << 23) * idz;
+    const float ox = (px - o.x) * idx, oy = (py - o.y) * idy, oz = (pz - o.z) * idz;
+    // conservative slack: covers the rounding of (p-o)*idir and of the per-child fma
+    const float eps = 4.76837158203125e-07f;   // 2^-21
+    const float padx = eps * (fabsf(ox) + 256.f * fabsf(sx));
+    const float pady = eps * (fabsf(oy) + 256.f * fabsf(sy));
+    const float padz = eps * (fabsf(oz) + 256.f * fabsf(sz));
+    const float oxn = ox - padx, oxf = ox + padx;
+    const float oyn = oy - pady, oyf = oy + pady;
+    const float ozn = oz - padz, ozf = oz + padz;
+
+    uint32_t hitmask = 0u;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int half = 0; half < 2; half++) {
+        const uint32_t meta4 = half ? n1.w : n1.z;
+        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t inner_mask4 = ((is_inner4 >> 4) & 0x01010101u) * 0xffu;
+        const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+        const uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
+        const uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
+        const uint32_t nearx = negx ? qhix : qlox, farx = negx ? qlox : qhix;
+        const uint32_t neary = negy ? qhiy : qloy, fary = negy ? qloy : qhiy;
+        const uint32_t nearz = negz ? qhiz : qloz, farz = negz ? qloz : qhiz;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int j = 0; j < 4; j++) {
+            const float t0x = byte_f(nearx, j) * sx + oxn, t1x = byte_f(farx, j) * sx + oxf;
+            const float t0y = byte_f(neary, j) * sy + oyn, t1y = byte_f(fary, j) * sy + oyf;
+            const float t0z = byte_f(nearz, j) * sz + ozn, t1z = byte_f(farz, j) * sz + ozf;
+            const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
+            const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
+            if (cmin <= cmax) {
+                const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu;
+                const uint32_t bi = (bit_index4 >> (8 * j)) & 0xffu;
+                hitmask |= cb << bi;
+            }
+        }
+    }
+    ng_x = n1.x;
+    ng_y = (hitmask & 0xff000000u) | (ew >> 24);
+    tg_x = n1.y;
+    tg_y = hitmask & 0x00ffffffu;
+}
+
+// Index (relative to the group's first child) of the next node of a node group; clears its hit bit.
+CRT_HD uint32_t next_child(uint32_t& ng_y, uint32_t octinv) {
+    const int bit = hi_bit(ng_y);
+    ng_y &= ~(1u << bit);
+    const uint32_t slot = (uint32_t)(bit - 24) ^ octinv;
+    return (uint32_t)pop_count(ng_y & ((1u << slot) - 1u) & 0xffu);
 }
 
 // ---- resumable traversal ---------------------------------------------------------------------------
@@ -134,75 +217,17 @@ struct Traverser {
 
     template <bool COUNT>
     CRT_HD bool step(const SceneView& sc, TravStack& st, TraceCounters* ctr, int postpone_lanes = CRT_POSTPONE_LANES) {
-        const bool negx = idx < 0.f, negy = idy < 0.f, negz = idz < 0.f;
-        const uint32_t octinv4 = octinv * 0x01010101u;
         uint32_t tg_x, tg_y;                  // primitive group: (first prim index, hits[23:0])
         if (ng_y & 0xff000000u) {
-            const int bit = hi_bit(ng_y);
-            ng_y &= ~(1u << bit);
-            if (ng_y & 0xff000000u) { st.x[sp] = ng_x; st.y[sp] = ng_y; sp++; }
-            const uint32_t slot = (uint32_t)(bit - 24) ^ octinv;
-            const uint32_t rel = (uint32_t)pop_count(ng_y & ((1u << slot) - 1u) & 0xffu);
-            const WideNode* node = sc.nodes + (ng_x + rel);
-            const u4 n0 = ld_u4(&node->n0);
-            const u4 n1 = ld_u4(&node->n1);
-            const u4 n2 = ld_u4(&node->n2);
-            const u4 n3 = ld_u4(&node->n3);
-            const u4 n4 = ld_u4(&node->n4);
+            const uint32_t base = ng_x;
+            uint32_t rest = ng_y;
+            const uint32_t rel = next_child(rest, octinv);
+            if (rest & 0xff000000u) { st.x[sp] = base; st.y[sp] = rest; sp++; }
             if (COUNT) ctr->nodes++;
 #ifdef CRT_NODE_HOOK
-            CRT_NODE_HOOK(ng_x + rel);
+            CRT_NODE_HOOK(base + rel);
 #endif
-            const float px = bits_f(n0.x), py = bits_f(n0.y), pz = bits_f(n0.z);
-            const uint32_t ew = n0.w;
-            const float sx = bits_f((ew & 0xffu) << 23) * idx;
-            const float sy = bits_f(((ew >> 8) & 0xffu) << 23) * idy;
-            const float sz = bits_f(((ew >> 16) & 0xffu) << 23) * idz;
-            const float ox = (px - o.x) * idx, oy = (py - o.y) * idy, oz = (pz - o.z) * idz;
-            // conservative slack: covers the rounding of (p-o)*idir and of the per-child fma
-            const float eps = 4.76837158203125e-07f;   // 2^-21
-            const float padx = eps * (fabsf(ox) + 256.f * fabsf(sx));
-            const float pady = eps * (fabsf(oy) + 256.f * fabsf(sy));
-            const float padz = eps * (fabsf(oz) + 256.f * fabsf(sz));
-            const float oxn = ox - padx, oxf = ox + padx;
-            const float oyn = oy - pady, oyf = oy + pady;
-            const float ozn = oz - padz, ozf = oz + padz;
-
-            uint32_t hitmask = 0u;
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-            for (int half = 0; half < 2; half++) {
-                const uint32_t meta4 = half ? n1.w : n1.z;
-                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-                const uint32_t inner_mask4 = ((is_inner4 >> 4) & 0x01010101u) * 0xffu;
-                const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
-                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-                const uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
-                const uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
-                const uint32_t nearx = negx ? qhix : qlox, farx = negx ? qlox : qhix;
-                const uint32_t neary = negy ? qhiy : qloy, fary = negy ? qloy : qhiy;
-                const uint32_t nearz = negz ? qhiz : qloz, farz = negz ? qloz : qhiz;
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-                for (int j = 0; j < 4; j++) {
-                    const float t0x = byte_f(nearx, j) * sx + oxn, t1x = byte_f(farx, j) * sx + oxf;
-                    const float t0y = byte_f(neary, j) * sy + oyn, t1y = byte_f(fary, j) * sy + oyf;
-                    const float t0z = byte_f(nearz, j) * sz + ozn, t1z = byte_f(farz, j) * sz + ozf;
-                    const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
-                    const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, rec.t));
-                    if (cmin <= cmax) {
-                        const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu;
-                        const uint32_t bi = (bit_index4 >> (8 * j)) & 0xffu;
-                        hitmask |= cb << bi;
-                    }
-                }
-            }
-            ng_x = n1.x;
-            ng_y = (hitmask & 0xff000000u) | (ew >> 24);
-            tg_x = n1.y;
-            tg_y = hitmask & 0x00ffffffu;
+            visit_node(sc.nodes + (base + rel), o, idx, idy, idz, tmin, rec.t, octinv, ng_x, ng_y, tg_x, tg_y);
         } else {
             tg_x = ng_x;
             tg_y = ng_y;

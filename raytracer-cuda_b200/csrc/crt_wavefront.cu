@@ -32,11 +32,12 @@ struct WavefrontState {
     float4* B = nullptr;
     float4* C = nullptr;
     uint32_t* queue[2] = {nullptr, nullptr};
-    uint32_t* qcount = nullptr;     // [0],[1] queue sizes, [2] iteration scratch
+    uint32_t* qcount = nullptr;     // [0],[1] queue sizes, [2] fetch cursor of extend
+    uint32_t* tile_count = nullptr; // per-tile survivor counts / offsets of the compaction
     uint32_t* h_qcount = nullptr;   // pinned
     size_t n = 0;
     int blocks_extend = 0, blocks_shade = 0;
-    int fetch_lanes = CRT_FETCH_LANES, postpone_lanes = CRT_POSTPONE_LANES;   // tuning knobs (env CRT_FETCH_LANES / CRT_POSTPONE_LANES)
+    int fetch_lanes = CRT_FETCH_LANES, postpone_lanes = CRT_POSTPONE_LANES, coop = 0;   // tuning knobs (env CRT_FETCH_LANES / CRT_POSTPONE_LANES)
     cudaEvent_t ev[3 * 16 + 2] = {};   // CRT_RENDER_TIME_KERNELS: begin pair + 3 events per iteration of a batch
 };
 
@@ -57,16 +58,96 @@ __device__ __forceinline__ void wf_store_rng(uint32_t* planes, size_t n, size_t 
     planes[3 * n + pix] = r.v3; planes[4 * n + pix] = r.v4; planes[5 * n + pix] = r.d;
 }
 
-// Warp-aggregated append: one atomic per warp, lanes ordered by ballot rank.
-__device__ __forceinline__ void queue_push(uint32_t* queue, uint32_t* count, bool keep, uint32_t value) {
-    const unsigned mask = __ballot_sync(0xffffffffu, keep);
-    if (mask == 0u) return;
-    const int lane = threadIdx.x & 31;
-    const int leader = __ffs(mask) - 1;
-    uint32_t base = 0;
-    if (lane == leader) base = atomicAdd(count, (uint32_t)__popc(mask));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (keep) queue[base + __popc(mask & ((1u << lane) - 1u))] = value;
+// ---- queue compaction -----------------------------------------------------------------------------
+// A pixel leaves the wavefront only when all its samples are done, so the queue shrinks slowly. shade marks
+// finished entries QUEUE_DEAD in place and every CRT_WF_BATCH iterations the queue is compacted with an
+// ORDER-PRESERVING ballot/popc scan: the queue stays sorted by pixel index, so the path-state and RNG-plane
+// accesses of extend and shade stay coalesced for the whole frame. (Appending survivors with one atomic per
+// warp, the first version, shuffles the queue a little at every departure; by iteration ~3000 of a 2000-spp
+// frame neighbouring entries came from unrelated pixels and shade ran 3x slower.)
+#define QUEUE_DEAD 0xffffffffu
+#define CRT_COMPACT_TILE 2048   // entries per CTA (256 threads x 8)
+
+__global__ void __launch_bounds__(256) k_compact_count(const uint32_t* queue, const uint32_t* qcount, int cur, uint32_t* tile_count) {
+    const uint32_t count = qcount[cur];
+    const uint32_t tile0 = blockIdx.x * CRT_COMPACT_TILE;
+    if (tile0 >= count) { if (threadIdx.x == 0) tile_count[blockIdx.x] = 0u; return; }
+    uint32_t n = 0;
+#pragma unroll
+    for (int k = 0; k < CRT_COMPACT_TILE / 256; k++) {
+        const uint32_t i = tile0 + k * 256 + threadIdx.x;
+        n += (i < count && queue[i] != QUEUE_DEAD) ? 1u : 0u;
+    }
+    __shared__ uint32_t warp_n[8];
+    n = __reduce_add_sync(0xffffffffu, n);
+    if ((threadIdx.x & 31) == 0) warp_n[threadIdx.x >> 5] = n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int k = 0; k < 8; k++) t += warp_n[k];
+        tile_count[blockIdx.x] = t;
+    }
+}
+
+// one CTA: exclusive scan of the tile counts in place, total -> qcount[cur ^ 1]
+__global__ void __launch_bounds__(1024) k_compact_scan(uint32_t* tile_count, int tiles, uint32_t* qcount, int cur) {
+    __shared__ uint32_t warp_sum[32];
+    __shared__ uint32_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0u;
+    __syncthreads();
+    for (int base = 0; base < tiles; base += 1024) {
+        const int i = base + threadIdx.x;
+        const uint32_t v = i < tiles ? tile_count[i] : 0u;
+        uint32_t incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xffffffffu, incl, d);
+            if ((threadIdx.x & 31) >= d) incl += u;
+        }
+        if ((threadIdx.x & 31) == 31) warp_sum[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = warp_sum[threadIdx.x];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t u = __shfl_up_sync(0xffffffffu, w, d);
+                if (threadIdx.x >= d) w += u;
+            }
+            warp_sum[threadIdx.x] = w;
+        }
+        __syncthreads();
+        const uint32_t carry = carry_s;
+        const uint32_t before = (threadIdx.x >> 5) ? warp_sum[(threadIdx.x >> 5) - 1] : 0u;
+        if (i < tiles) tile_count[i] = carry + before + incl - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = carry + before + incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { qcount[cur ^ 1] = carry_s; qcount[2] = 0u; }
+}
+
+__global__ void __launch_bounds__(256) k_compact_scatter(const uint32_t* queue_in, uint32_t* queue_out, const uint32_t* qcount, int cur,
+                                                         const uint32_t* tile_offset) {
+    const uint32_t count = qcount[cur];
+    const uint32_t tile0 = blockIdx.x * CRT_COMPACT_TILE;
+    if (tile0 >= count) return;
+    __shared__ uint32_t warp_n[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t out = tile_offset[blockIdx.x];
+    for (int k = 0; k < CRT_COMPACT_TILE / 256; k++) {
+        const uint32_t i = tile0 + k * 256 + threadIdx.x;
+        const uint32_t v = i < count ? queue_in[i] : QUEUE_DEAD;
+        const bool keep = v != QUEUE_DEAD;
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) warp_n[warp] = (uint32_t)__popc(m);
+        __syncthreads();
+        uint32_t before = 0, all = 0;
+#pragma unroll
+        for (int q = 0; q < 8; q++) { const uint32_t c = warp_n[q]; if (q < warp) before += c; all += c; }
+        if (keep) queue_out[out + before + (uint32_t)__popc(m & ((1u << lane) - 1u))] = v;
+        out += all;
+        __syncthreads();
+    }
 }
 
 // ---- begin: first camera ray of every pixel, queue = all pixels ---------------------------------
@@ -92,20 +173,39 @@ __global__ void __launch_bounds__(256) k_wf_begin(RenderArgs a, WfView w, uint32
 }
 
 // ---- extend: closest hit for every queued ray -------------------------------------------------------
-// Persistent warps with dynamic fetch: a warp keeps up to 32 rays in flight and all its lanes advance
-// their traversals one wide node at a time; when CRT_FETCH_LANES lanes have finished, they take the next
-// rays from the queue together (one atomic per refill), so a long ray (one that wanders through the mesh)
-// does not hold 31 finished lanes idle. qcount[2] is the shared fetch cursor (reset by begin / shade).
-template <bool COUNT>
+// Persistent warps, two ideas against SIMT divergence (ncu on the one-ray-per-thread version showed 8 of
+// 32 lanes active per instruction):
+//  1. dynamic fetch: a warp keeps up to 32 rays in flight; when `fetch_lanes` lanes have finished they
+//     take the next rays from the queue together (one atomic per refill), so a long ray (one that wanders
+//     through the mesh) does not hold 31 finished lanes idle. qcount[2] is the shared fetch cursor.
+//  2. warp-cooperative primitive tests: a node visit leaves each lane with 0..n primitives to test, so a
+//     per-lane loop runs with ~6 lanes. Instead the (ray, primitive) pairs of the whole warp are pooled in
+//     shared memory and dealt out one pair per lane; a hit updates the owning ray's closest hit with a
+//     64-bit shared-memory atomicMin on (t bits << 32 | ~id), which is exactly the order-independent
+//     acceptance rule of test_prim (smaller t, then larger primitive id).
+struct WarpPool {
+    float ray[6][32];                 // o.xyz, d.xyz of the lane's ray
+    unsigned long long best[32];      // (t bits << 32) | (0xffffffff - id)
+    uint32_t win[32];                 // index of the winning primitive record (0xffffffff = none)
+    uint32_t list[256];               // (owner lane << 27) | primitive record index
+};
+
+template <bool COUNT, bool COOP>
 __global__ void __launch_bounds__(256) k_wf_extend(SceneView scene, WfView w, const uint32_t* queue, uint32_t* qcount, int cur,
                                                    unsigned long long* counters, int fetch_lanes, int postpone_lanes) {
+    (void)postpone_lanes;
+    __shared__ WarpPool pools[8];
+    WarpPool& S = pools[threadIdx.x >> 5];
     const uint32_t count = qcount[cur];
     const int lane = threadIdx.x & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    TraceCounters ctr;
-    ctr.nodes = 0; ctr.prims = 0;
-    Traverser tr;
+    const float tmin = 0.001f;
+    uint32_t c_nodes = 0, c_prims = 0, c_rays = 0;
     TravStack st;
+    vec3 o = mk3(0.f, 0.f, 0.f);
+    float idx = 1.f, idy = 1.f, idz = 1.f;
+    uint32_t octinv = 0, ng_x = 0, ng_y = 0;
+    int sp = 0;
     bool has_ray = false, exhausted = false;
     uint32_t pix = 0;
     while (true) {
@@ -117,45 +217,150 @@ __global__ void __launch_bounds__(256) k_wf_extend(SceneView scene, WfView w, co
             base = __shfl_sync(0xffffffffu, base, leader);
             if (base + (uint32_t)n >= count) exhausted = true;
             const uint32_t i = base + (uint32_t)__popc(idle & lt_mask);
-            if (!has_ray && i < count) {
-                pix = queue[i];
+            if (!has_ray && i < count) pix = queue[i];
+            if (!has_ray && i < count && pix != QUEUE_DEAD) {
                 const float4 A = w.A[pix], B = w.B[pix];
-                tr.begin(mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), 0.001f, INFINITY);
+                o = mk3(A.x, A.y, A.z);
+                const float tiny = 1e-20f;   // zero direction components nudged for the box tests only
+                const float ddx = fabsf(B.x) < tiny ? (B.x < 0.f ? -tiny : tiny) : B.x;
+                const float ddy = fabsf(B.y) < tiny ? (B.y < 0.f ? -tiny : tiny) : B.y;
+                const float ddz = fabsf(B.z) < tiny ? (B.z < 0.f ? -tiny : tiny) : B.z;
+                idx = 1.0f / ddx; idy = 1.0f / ddy; idz = 1.0f / ddz;
+                octinv = (ddx < 0.f ? 0u : 4u) | (ddy < 0.f ? 0u : 2u) | (ddz < 0.f ? 0u : 1u);
+                sp = 0; ng_x = 0u; ng_y = 0x80000000u;
+                S.ray[0][lane] = A.x; S.ray[1][lane] = A.y; S.ray[2][lane] = A.z;
+                S.ray[3][lane] = B.x; S.ray[4][lane] = B.y; S.ray[5][lane] = B.z;
+                S.best[lane] = ((unsigned long long)0x7f800000u << 32) | 0xffffffffull;   // t = +inf
+                S.win[lane] = 0xffffffffu;
                 has_ray = true;
+                c_rays++;
             }
             idle = __ballot_sync(0xffffffffu, !has_ray);
         }
-        if (idle == 0xffffffffu) break;
+        if (idle == 0xffffffffu) {
+            if (exhausted) break;
+            continue;   // a refill that met only finished (dead) queue entries: fetch again
+        }
+
+        // node round: every lane with a ray visits its next wide node, or finishes
+        uint32_t tg_x = 0u, tg_y = 0u;
         if (has_ray) {
-            if (tr.step<COUNT>(scene, st, &ctr, postpone_lanes)) {
-                float2* c = reinterpret_cast<float2*>(&w.C[pix]);
-                *c = make_float2(tr.rec.id >= 0 ? tr.rec.t : -1.f, __uint_as_float(tr.rec.prim));
-                has_ray = false;
+            if ((ng_y & 0xff000000u) == 0u) {
+                if (sp == 0) {
+                    const uint32_t win = S.win[lane];
+                    const float t = __uint_as_float((uint32_t)(S.best[lane] >> 32));
+                    float2* c = reinterpret_cast<float2*>(&w.C[pix]);
+                    *c = make_float2(win != 0xffffffffu ? t : -1.f, __uint_as_float(win));
+                    has_ray = false;
+                } else {
+                    sp--;
+                    ng_x = st.x[sp];
+                    ng_y = st.y[sp];
+                }
+            }
+        }
+        __syncwarp();   // reconverge: without it the lanes that popped the stack visit their node in a second pass
+        if (has_ray) {
+            {
+                const uint32_t base = ng_x;
+                uint32_t rest = ng_y;
+                const uint32_t rel = next_child(rest, octinv);
+                if (rest & 0xff000000u) { st.x[sp] = base; st.y[sp] = rest; sp++; }
+                if (COUNT) c_nodes++;
+                const float tmax = __uint_as_float((uint32_t)(S.best[lane] >> 32));
+                visit_node(scene.nodes + (base + rel), o, idx, idy, idz, tmin, tmax, octinv, ng_x, ng_y, tg_x, tg_y);
+            }
+        }
+
+        __syncwarp();
+        if (!COOP) {   // comparison variant: every lane loops over its own primitives
+            if (tg_y) {
+                const vec3 rd = mk3(S.ray[3][lane], S.ray[4][lane], S.ray[5][lane]);
+                HitRec rec;
+                const unsigned long long b = S.best[lane];
+                rec.t = __uint_as_float((uint32_t)(b >> 32));
+                rec.id = (int32_t)(0xffffffffu - (uint32_t)b);
+                rec.prim = S.win[lane];
+                if (rec.prim == 0xffffffffu) rec.id = -1;
+                bool any = false;
+                while (tg_y) {
+                    const int i = 31 - __clz((int)tg_y);
+                    tg_y &= ~(1u << i);
+                    if (COUNT) c_prims++;
+                    any |= test_prim(scene.prims, tg_x + (uint32_t)i, o, rd, tmin, rec);
+                }
+                if (any) {
+                    S.best[lane] = ((unsigned long long)__float_as_uint(rec.t) << 32) | (unsigned long long)(0xffffffffu - (uint32_t)rec.id);
+                    S.win[lane] = rec.prim;
+                }
+            }
+            __syncwarp();
+            continue;
+        }
+        // cooperative primitive rounds: pool the warp's (ray, primitive) pairs, one pair per lane
+        while (true) {
+            int cnt = __popc(tg_y);
+            if (cnt > 8) cnt = 8;
+            int incl = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += v;
+            }
+            const int total = __shfl_sync(0xffffffffu, incl, 31);
+            if (total == 0) break;
+            int pos = incl - cnt;
+            for (int j = 0; j < cnt; j++) {
+                const int i = 31 - __clz((int)tg_y);
+                tg_y &= ~(1u << i);
+                S.list[pos++] = ((uint32_t)lane << 27) | (tg_x + (uint32_t)i);
+            }
+            __syncwarp();
+            for (int k0 = 0; k0 < total; k0 += 32) {
+                const int k = k0 + lane;
+                bool hit = false;
+                unsigned long long key = 0ull;
+                uint32_t owner = 0u, pi = 0u;
+                if (k < total) {
+                    const uint32_t e = S.list[k];
+                    owner = e >> 27;
+                    pi = e & 0x07ffffffu;
+                    const vec3 ro = mk3(S.ray[0][owner], S.ray[1][owner], S.ray[2][owner]);
+                    const vec3 rd = mk3(S.ray[3][owner], S.ray[4][owner], S.ray[5][owner]);
+                    const float tmax = __uint_as_float((uint32_t)(S.best[owner] >> 32));
+                    float t;
+                    int32_t id;
+                    if (COUNT) c_prims++;
+                    hit = prim_hit(scene.prims, pi, ro, rd, tmin, tmax, t, id);
+                    if (hit) {
+                        key = ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(0xffffffffu - (uint32_t)id);
+                        atomicMin(&S.best[owner], key);
+                    }
+                }
+                __syncwarp();
+                if (hit && S.best[owner] == key) S.win[owner] = pi;
+                __syncwarp();
             }
         }
     }
+    c_rays = __reduce_add_sync(0xffffffffu, c_rays);
+    if (lane == 0 && c_rays) atomicAdd(&counters[0], (unsigned long long)c_rays);
     if (COUNT) {
-        unsigned long long nodes = ctr.nodes, prims = ctr.prims;
-        for (int o = 16; o > 0; o >>= 1) { nodes += __shfl_xor_sync(0xffffffffu, nodes, o); prims += __shfl_xor_sync(0xffffffffu, prims, o); }
-        if (lane == 0 && (nodes | prims)) { atomicAdd(&counters[2], nodes); atomicAdd(&counters[3], prims); }
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        counters[0] += count;        // one ray per queued path; only this thread writes counters[0]
-        qcount[cur ^ 1] = 0u;         // the other queue is free again: shade will append to it
+        c_nodes = __reduce_add_sync(0xffffffffu, c_nodes);
+        c_prims = __reduce_add_sync(0xffffffffu, c_prims);
+        if (lane == 0 && (c_nodes | c_prims)) { atomicAdd(&counters[2], (unsigned long long)c_nodes); atomicAdd(&counters[3], (unsigned long long)c_prims); }
     }
 }
 
 // ---- shade: consume the hit, continue / finish / regenerate, Russian roulette, compact -----------------
-__global__ void __launch_bounds__(256) k_wf_shade(RenderArgs a, WfView w, const uint32_t* queue_in, uint32_t* queue_out,
-                                                  uint32_t* qcount, int cur) {
+__global__ void __launch_bounds__(256) k_wf_shade(RenderArgs a, WfView w, uint32_t* queue, uint32_t* qcount, int cur) {
     const uint32_t count = qcount[cur];
     const uint32_t rounded = (count + 31u) & ~31u;
     const size_t n = (size_t)a.rc.width * a.rc.height;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
         bool keep = false;
-        uint32_t pix = 0;
-        if (i < count) {
-            pix = queue_in[i];
+        uint32_t pix = i < count ? queue[i] : QUEUE_DEAD;
+        if (pix != QUEUE_DEAD) {
             const float4 A = w.A[pix], B = w.B[pix], C = w.C[pix];
             vec3 o = mk3(A.x, A.y, A.z), d = mk3(B.x, B.y, B.z), thr = mk3(A.w, B.w, C.z);
             const uint32_t book = __float_as_uint(C.w);
@@ -225,9 +430,10 @@ __global__ void __launch_bounds__(256) k_wf_shade(RenderArgs a, WfView w, const 
                 w.B[pix] = make_float4(d.x, d.y, d.z, thr.y);
                 float2* c2 = reinterpret_cast<float2*>(&w.C[pix]) + 1;
                 *c2 = make_float2(thr.z, __uint_as_float((uint32_t)sample | ((uint32_t)bounce << 24)));
+            } else {
+                queue[i] = QUEUE_DEAD;   // all samples of this pixel are done
             }
         }
-        queue_push(queue_out, &qcount[cur ^ 1], keep, pix);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) qcount[2] = 0u;   // fetch cursor of the next extend
 }
@@ -241,11 +447,13 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
     if (e == cudaSuccess) e = cudaMalloc(&s->queue[0], s->n * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaMalloc(&s->queue[1], s->n * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaMalloc(&s->qcount, 4 * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMalloc(&s->tile_count, ((s->n + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE + 1) * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaMallocHost(&s->h_qcount, 4 * sizeof(uint32_t));
     int be = 0, bs = 0;
-    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&be, k_wf_extend<false>, 256, 0);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&be, k_wf_extend<false, true>, 256, 0);
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade, 256, 0);
     if (const char* v = getenv("CRT_FETCH_LANES")) s->fetch_lanes = atoi(v);
+    if (const char* v = getenv("CRT_COOP")) s->coop = atoi(v);
     if (const char* v = getenv("CRT_POSTPONE_LANES")) s->postpone_lanes = atoi(v);
     if (s->fetch_lanes < 1) s->fetch_lanes = 1;
     if (s->fetch_lanes > 32) s->fetch_lanes = 32;
@@ -259,7 +467,7 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
 
 void wavefront_destroy(WavefrontState* s) {
     if (!s) return;
-    cudaFree(s->A); cudaFree(s->B); cudaFree(s->C); cudaFree(s->queue[0]); cudaFree(s->queue[1]); cudaFree(s->qcount);
+    cudaFree(s->A); cudaFree(s->B); cudaFree(s->C); cudaFree(s->queue[0]); cudaFree(s->queue[1]); cudaFree(s->qcount); cudaFree(s->tile_count);
     if (s->h_qcount) cudaFreeHost(s->h_qcount);
     for (cudaEvent_t ev : s->ev) if (ev) cudaEventDestroy(ev);
     delete s;
@@ -290,14 +498,23 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
     while (e == cudaSuccess && it < max_iters) {
         for (int b = 0; b < batch; b++) {
             if (timed) cudaEventRecord(ws->ev[3 * b], stream);
-            if (counted) k_wf_extend<true><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
-            else k_wf_extend<false><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
+            if (counted) k_wf_extend<true, true><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
+            else if (ws->coop) k_wf_extend<false, true><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
+            else k_wf_extend<false, false><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
             if (timed) cudaEventRecord(ws->ev[3 * b + 1], stream);
-            k_wf_shade<<<grid_s, 256, 0, stream>>>(a, w, ws->queue[cur], ws->queue[cur ^ 1], ws->qcount, cur);
+            k_wf_shade<<<grid_s, 256, 0, stream>>>(a, w, ws->queue[cur], ws->qcount, cur);
             if (timed) cudaEventRecord(ws->ev[3 * b + 2], stream);
             nl += 2;
-            cur ^= 1;
             it++;
+        }
+        // order-preserving compaction of the survivors into the other queue
+        {
+            const int tiles = (int)((ws->n + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE);
+            k_compact_count<<<tiles, 256, 0, stream>>>(ws->queue[cur], ws->qcount, cur, ws->tile_count);
+            k_compact_scan<<<1, 1024, 0, stream>>>(ws->tile_count, tiles, ws->qcount, cur);
+            k_compact_scatter<<<tiles, 256, 0, stream>>>(ws->queue[cur], ws->queue[cur ^ 1], ws->qcount, cur, ws->tile_count);
+            nl += 3;
+            cur ^= 1;
         }
         e = cudaGetLastError();
         if (e != cudaSuccess) break;
