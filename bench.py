@@ -42,8 +42,8 @@ def parse():
     ap.add_argument("--height", type=int, default=1440)
     ap.add_argument("--spp", type=int, default=2000)
     ap.add_argument("--bounces", type=int, default=20)
-    ap.add_argument("--ref-spp", type=int, default=32, help="bounded sample of the workload for the reference arm")
-    ap.add_argument("--cpu-sample", default="512x288x8", help="oracle sample WxHxSPP (centre window of the frame)")
+    ap.add_argument("--ref-spp", type=int, default=128, help="bounded sample of the workload for the reference arm")
+    ap.add_argument("--cpu-sample", default="512x288x256", help="oracle sample WxHxSPP (centre window of the frame)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -161,6 +161,7 @@ def main():
         return run_reference(args)
     import torch
     crt = importlib.import_module("raytracer-cuda_b200")
+    mg = importlib.import_module("raytracer-cuda_b200.multigpu")
     crt.load_library()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -179,19 +180,15 @@ def main():
     r = crt.Renderer(W, H, device=local, mode=mode)
     r.set_scene(sc)
     r.update_camera(cam)
-    r.initialize(SEED, rank * W * H)          # disjoint cuRAND subsequences per rank
+    r.initialize(SEED, mg.subsequence_base(rank, W, H))     # disjoint cuRAND subsequences per rank
     build = r.stats()
-    my_spp = args.spp // world + (1 if rank < args.spp % world else 0)
+    my_spp = mg.shard_spp(args.spp, world, rank)
     flags = crt.RENDER_NO_TONEMAP if world > 1 else 0
-
-    # accumulation buffer as a torch tensor (device pointer borrowed from the library) for the NCCL reduce
-    acc_t = None
-    if world > 1:
-        class _Ptr:
-            pass
-        holder = _Ptr()
-        holder.__cuda_array_interface__ = {"shape": (H, W, 4), "typestr": "<f4", "data": (r.accum_device_ptr(), False), "version": 3}
-        acc_t = torch.as_tensor(holder, device=torch.device("cuda", local))
+    # the library launches on torch's current stream from here on, so torch events and the NCCL reduce
+    # order with the render kernels (torch.cuda.Event only sees torch's current stream)
+    stream = torch.cuda.current_stream()
+    r.set_stream(stream.cuda_stream)
+    acc_t = mg.accum_as_tensor(torch, r.accum_device_ptr(), H, W, local) if world > 1 else None
     host_img = np.empty((H, W, 4), np.uint8)
 
     def sync_all():
@@ -205,55 +202,53 @@ def main():
             r.update_camera(cam)              # per-frame host->device input, like CUDARenderer::updateCamera
         st = r.render(my_spp, args.bounces, flags=flags | (crt.RENDER_TIME_KERNELS if time_kernels else 0))
         if dist is not None:
-            dist.reduce(acc_t, dst=0, op=dist.ReduceOp.SUM)
+            mg.reduce_accum(acc_t, dist, dst=0)
             if rank == 0:
                 r.tonemap()
         if e2e and rank == 0:
             r.image_rgba8(host_img)           # device->host frame, like WindowManager::drawFrame
         return st
 
+    def timed(n, **kw):
+        """n steps bracketed by barrier + synchronize, timed with CUDA events on the launching stream."""
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        acc = {"rays": 0, "launches": 0, "ext_ms": 0.0, "shade_ms": 0.0, "ext_launches": 0}
+        sync_all()
+        ev0.record(stream)
+        for _ in range(n):
+            st = step(**kw)
+            acc["rays"] += int(st.rays)
+            acc["launches"] += int(st.kernel_launches) + (1 if world > 1 and rank == 0 else 0)
+            acc["ext_ms"] += st.extend_ms
+            acc["shade_ms"] += st.shade_ms
+            acc["ext_launches"] += int(st.extend_launches)
+        ev1.record(stream)
+        sync_all()
+        acc["ms"] = ev0.elapsed_time(ev1)
+        return acc
+
     for _ in range(args.warmup):
         step()
-    sync_all()
     clk = ClockSampler(local)
     if rank == 0:
         clk.start()
-    rays = launches = 0
-    ext_ms = shade_ms = 0.0
-    ext_launches = 0
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        st = step(time_kernels=True)
-        rays += int(st.rays)
-        launches += int(st.kernel_launches) + (1 if world > 1 and rank == 0 else 0)
-        ext_ms += st.extend_ms
-        shade_ms += st.shade_ms
-        ext_launches += int(st.extend_launches)
-    sync_all()
-    dt = time.perf_counter() - t0
+    main_run = timed(args.steps)
     clocks = clk.finish() if rank == 0 else None
-
+    # per-kernel-class times (events between the launches perturb the pipeline a little: separate, untimed-for-value pass)
+    k_run = timed(1, time_kernels=True)
     # e2e: the same frames through the public API with host buffers inside the timed region
-    sync_all()
-    t1 = time.perf_counter()
-    e_rays = 0
-    for _ in range(args.steps):
-        e_rays += int(step(e2e=True).rays)
-    sync_all()
-    dt_e2e = time.perf_counter() - t1
+    e_run = timed(args.steps, e2e=True)
 
-    tot = torch.tensor([float(rays), float(e_rays), dt, dt_e2e, float(launches)], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([float(main_run["rays"]), float(e_run["rays"]), float(main_run["launches"])], dtype=torch.float64, device="cuda")
+    mx = torch.tensor([main_run["ms"], e_run["ms"]], dtype=torch.float64, device="cuda")
     if dist is not None:
-        mx = tot.clone()
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        rays_all, e_rays_all, launches_all = tot[0].item(), tot[1].item(), tot[4].item()
-        dt, dt_e2e = mx[2].item(), mx[3].item()
-    else:
-        rays_all, e_rays_all, launches_all = float(rays), float(e_rays), float(launches)
+    rays_all, e_rays_all, launches_all = tot[0].item(), tot[1].item(), tot[2].item()
+    dt, dt_e2e = mx[0].item() * 1e-3, mx[1].item() * 1e-3
 
     if rank == 0:
-        # bytes per ray of the dominant kernel from an instrumented (untimed) bounded render
+        # algorithmic bytes per ray of the dominant kernel: counted by an instrumented (untimed) bounded render
         r.initialize(SEED, 0)
         c = r.render(2, args.bounces, flags=flags, counted=True)
         n_bar, t_bar = c.nodes_fetched / c.rays, c.prims_tested / c.rays
@@ -261,21 +256,33 @@ def main():
         b_ray = 80.0 * n_bar + 48.0 * t_bar + rec_bytes
         peaks, how = measured_peaks()
         kernel = "k_wf_extend" if args.mode == "wavefront" else "k_render_mega"
-        achieved = (b_ray * rays) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else None
+        ext_ms, ext_launches = k_run["ext_ms"], max(k_run["ext_launches"], 1)
+        achieved = (b_ray * k_run["rays"]) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else None
+        traffic, traffic_src = None, None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            try:
+                tj = json.load(open(tp))
+                traffic, traffic_src = tj.get(kernel, {}).get("dram_bytes_per_launch"), tj.get(kernel, {}).get("source")
+            except Exception:
+                pass
         roof = {"bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": (achieved / peaks["hbm_gbs"]) if achieved else None, "traffic": None, "peak_source": how,
+                "frac": (achieved / peaks["hbm_gbs"]) if achieved else None, "traffic": traffic, "traffic_source": traffic_src,
+                "peak_source": how + " (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)",
                 "bytes_per_ray": b_ray, "nodes_per_ray": n_bar, "prims_per_ray": t_bar,
-                "kernel_ms_per_launch": ext_ms / max(ext_launches, 1), "kernel_launches": ext_launches,
-                "kernel_share_of_step": ext_ms / (dt * 1e3), "shade_ms_per_step": shade_ms / args.steps,
-                "note": "algorithmic bytes are served mostly from L1/L2 (the BVH is cache resident); see DESIGN.md"}
+                "algorithmic_bytes_per_launch": b_ray * k_run["rays"] / ext_launches,
+                "kernel_ms_per_launch": ext_ms / ext_launches, "kernel_launches_per_step": k_run["ext_launches"],
+                "kernel_share_of_step": ext_ms / k_run["ms"], "shade_ms_per_step": k_run["shade_ms"],
+                "note": "extend is instruction-issue bound, not DRAM bound: nodes and triangles (4.3 MB) are served from L1/L2, "
+                        "so achieved/peak compares cache-served algorithmic bytes with the HBM copy peak; see DESIGN.md §3/§6"}
         cpu = None if args.no_cpu_baseline or world > 1 else cpu_baseline(crt, args)
         value = rays_all / dt / 1e6
         line = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
-                "config": {"workload": "%s %dx%d %d spp %d bounces (BASELINE.json configs[1]); spp sharded over ranks; "
-                                       "per-step state %d MB > L2 so no L2 flush between steps" %
-                                       (args.scene, W, H, args.spp, args.bounces, (24 + 16 + 48 + 8) * W * H // 2 ** 20),
+                "config": {"workload": "%s %dx%d %d spp %d bounces (BASELINE.json configs[1]); one step = one frame; spp sharded over "
+                                       "ranks, one NCCL reduce of the float4 buffer per frame; per-step state %d MB > L2 (126 MB), so no L2 "
+                                       "flush between steps" % (args.scene, W, H, args.spp, args.bounces, (24 + 16 + 48 + 8) * W * H // 2 ** 20),
                            "mode": args.mode, "triangles": sc.num_triangles, "spheres": sc.num_spheres, "seed": SEED,
                            "bvh_nodes": int(build.bvh_nodes), "bvh_build_ms": build.bvh_build_ms, "rng_init_ms": build.rng_init_ms},
                 "frame_ms": dt / args.steps * 1e3, "rays_per_step": rays_all / args.steps,

@@ -250,6 +250,12 @@ int crt_get_stats(crt_ctx* ctx, crt_stats* out);
 /* CUDA stream (cudaStream_t) the context launches on, for event timing by the caller. */
 int crt_get_stream(crt_ctx* ctx, void** out_stream);
 
+/* Make the context launch on the caller's stream (cudaStream_t) instead of its own, so that the caller's
+ * events and collectives (e.g. the multi-GPU reduce of the accumulation buffer) order with the render
+ * without extra synchronisation. NULL restores the context's own stream. The legacy default stream of the
+ * reference (src/CUDARenderer.cuh:57) is what this generalises. */
+int crt_set_stream(crt_ctx* ctx, void* stream);
+
 /* ---- built-in procedural scenes (BASELINE.json configs; assets/ is absent upstream) ---
  * names: "cornell" (C1), "cornell_blob" (C2/C5), "spheres" (C3), "terrain" (C4).
  * param: scene-specific size knob (0 = default; blob/terrain: grid resolution scale).

@@ -103,6 +103,7 @@ def load_library():
         "crt_set_rng_state": (C.c_int, [P, P]),
         "crt_get_stats": (C.c_int, [P, C.POINTER(Stats)]),
         "crt_get_stream": (C.c_int, [P, C.POINTER(P)]),
+        "crt_set_stream": (C.c_int, [P, P]),
         "crt_scene_builtin": (C.c_int, [C.c_char_p, C.c_int32, C.POINTER(C.POINTER(Scene)), C.POINTER(Camera)]),
         "crt_scene_free": (None, [C.POINTER(Scene)]),
         "crt_scene_load_obj": (C.c_int, [C.POINTER(C.c_char_p), C.c_int32, C.c_int32, C.POINTER(C.POINTER(Scene)),
@@ -123,7 +124,7 @@ def load_library():
 API_FUNCTIONS = ["crt_api_version", "crt_create", "crt_destroy", "crt_last_error", "crt_init_rng", "crt_set_scene",
                  "crt_set_camera", "crt_render", "crt_render_counted", "crt_primary_ids", "crt_get_image_rgba8",
                  "crt_get_accum", "crt_set_accum", "crt_tonemap", "crt_get_rng_state", "crt_set_rng_state",
-                 "crt_get_stats", "crt_get_stream", "crt_scene_builtin", "crt_scene_free", "crt_scene_load_obj",
+                 "crt_get_stats", "crt_get_stream", "crt_set_stream", "crt_scene_builtin", "crt_scene_free", "crt_scene_load_obj",
                  "crt_write_ppm", "crt_write_pfm", "crt_checkpoint_save", "crt_checkpoint_load"]
 
 
@@ -313,6 +314,9 @@ class Renderer:
         p = C.c_void_p()
         self._check(self.lib.crt_get_stream(self._ctx, C.byref(p)))
         return p.value
+
+    def set_stream(self, stream_ptr):
+        self._check(self.lib.crt_set_stream(self._ctx, C.c_void_p(stream_ptr)))
 
     def write_ppm(self, path):
         self._check(self.lib.crt_write_ppm(self._ctx, path.encode()))

@@ -23,6 +23,7 @@ struct crt_ctx {
     crt_config cfg{};
     int num_sms = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t own_stream = nullptr;   // created by crt_create; `stream` may be replaced by crt_set_stream
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // frame buffers
     FrameBuffers fb{};
@@ -110,7 +111,8 @@ int crt_create(crt_ctx** out_ctx, const crt_config* cfg) {
     if (ctx->cfg.bvh_leaf_max <= 0) ctx->cfg.bvh_leaf_max = 3;
     ctx->num_sms = prop.multiProcessorCount;
     const size_t n = (size_t)cfg->width * cfg->height;
-    cudaError_t e2 = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    cudaError_t e2 = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
+    ctx->stream = ctx->own_stream;
     if (e2 == cudaSuccess) e2 = cudaEventCreate(&ctx->ev0);
     if (e2 == cudaSuccess) e2 = cudaEventCreate(&ctx->ev1);
     if (e2 == cudaSuccess) e2 = cudaMalloc(&ctx->fb.rng, n * 6 * sizeof(uint32_t));
@@ -139,7 +141,7 @@ void crt_destroy(crt_ctx* ctx) {
     cudaFree(ctx->fb.rng); cudaFree(ctx->fb.accum); cudaFree(ctx->fb.rgba8); cudaFree(ctx->fb.counters);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
-    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     (void)cudaGetLastError();
     delete ctx;
 }
@@ -342,6 +344,14 @@ int crt_set_rng_state(crt_ctx* ctx, const uint32_t* host) {
 int crt_get_stats(crt_ctx* ctx, crt_stats* out) {
     if (!ctx || !out) return CRT_E_INVALID;
     *out = ctx->stats;
+    return CRT_OK;
+}
+
+int crt_set_stream(crt_ctx* ctx, void* stream) {
+    if (!ctx) return CRT_E_INVALID;
+    CU(cudaSetDevice(ctx->cfg.device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->stream = stream ? (cudaStream_t)stream : ctx->own_stream;
     return CRT_OK;
 }
 
