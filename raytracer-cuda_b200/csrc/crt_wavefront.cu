@@ -24,7 +24,7 @@
 namespace crt {
 
 #ifndef CRT_FETCH_LANES
-#define CRT_FETCH_LANES 8
+#define CRT_FETCH_LANES 12
 #endif
 
 struct WavefrontState {
@@ -202,7 +202,9 @@ __global__ void __launch_bounds__(256) k_wf_extend(SceneView scene, WfView w, co
     const float tmin = 0.001f;
     uint32_t c_nodes = 0, c_prims = 0, c_rays = 0;
     TravStack st;
-    vec3 o = mk3(0.f, 0.f, 0.f);
+    vec3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
+    HitRec rec;
+    rec.t = INFINITY; rec.prim = 0u; rec.id = -1;
     float idx = 1.f, idy = 1.f, idz = 1.f;
     uint32_t octinv = 0, ng_x = 0, ng_y = 0;
     int sp = 0;
@@ -221,6 +223,8 @@ __global__ void __launch_bounds__(256) k_wf_extend(SceneView scene, WfView w, co
             if (!has_ray && i < count && pix != QUEUE_DEAD) {
                 const float4 A = w.A[pix], B = w.B[pix];
                 o = mk3(A.x, A.y, A.z);
+                d = mk3(B.x, B.y, B.z);
+                rec.t = INFINITY; rec.prim = 0u; rec.id = -1;
                 const float tiny = 1e-20f;   // zero direction components nudged for the box tests only
                 const float ddx = fabsf(B.x) < tiny ? (B.x < 0.f ? -tiny : tiny) : B.x;
                 const float ddy = fabsf(B.y) < tiny ? (B.y < 0.f ? -tiny : tiny) : B.y;
@@ -228,10 +232,12 @@ __global__ void __launch_bounds__(256) k_wf_extend(SceneView scene, WfView w, co
                 idx = 1.0f / ddx; idy = 1.0f / ddy; idz = 1.0f / ddz;
                 octinv = (ddx < 0.f ? 0u : 4u) | (ddy < 0.f ? 0u : 2u) | (ddz < 0.f ? 0u : 1u);
                 sp = 0; ng_x = 0u; ng_y = 0x80000000u;
-                S.ray[0][lane] = A.x; S.ray[1][lane] = A.y; S.ray[2][lane] = A.z;
-                S.ray[3][lane] = B.x; S.ray[4][lane] = B.y; S.ray[5][lane] = B.z;
-                S.best[lane] = ((unsigned long long)0x7f800000u << 32) | 0xffffffffull;   // t = +inf
-                S.win[lane] = 0xffffffffu;
+                if (COOP) {
+                    S.ray[0][lane] = A.x; S.ray[1][lane] = A.y; S.ray[2][lane] = A.z;
+                    S.ray[3][lane] = B.x; S.ray[4][lane] = B.y; S.ray[5][lane] = B.z;
+                    S.best[lane] = ((unsigned long long)0x7f800000u << 32) | 0xffffffffull;   // t = +inf
+                    S.win[lane] = 0xffffffffu;
+                }
                 has_ray = true;
                 c_rays++;
             }
@@ -242,61 +248,27 @@ __global__ void __launch_bounds__(256) k_wf_extend(SceneView scene, WfView w, co
             continue;   // a refill that met only finished (dead) queue entries: fetch again
         }
 
-        // node round: every lane with a ray visits its next wide node, or finishes
+        // node round: every lane with a ray visits its next wide node (a lane with a ray always has one pending)
         uint32_t tg_x = 0u, tg_y = 0u;
         if (has_ray) {
-            if ((ng_y & 0xff000000u) == 0u) {
-                if (sp == 0) {
-                    const uint32_t win = S.win[lane];
-                    const float t = __uint_as_float((uint32_t)(S.best[lane] >> 32));
-                    float2* c = reinterpret_cast<float2*>(&w.C[pix]);
-                    *c = make_float2(win != 0xffffffffu ? t : -1.f, __uint_as_float(win));
-                    has_ray = false;
-                } else {
-                    sp--;
-                    ng_x = st.x[sp];
-                    ng_y = st.y[sp];
-                }
-            }
-        }
-        __syncwarp();   // reconverge: without it the lanes that popped the stack visit their node in a second pass
-        if (has_ray) {
-            {
-                const uint32_t base = ng_x;
-                uint32_t rest = ng_y;
-                const uint32_t rel = next_child(rest, octinv);
-                if (rest & 0xff000000u) { st.x[sp] = base; st.y[sp] = rest; sp++; }
-                if (COUNT) c_nodes++;
-                const float tmax = __uint_as_float((uint32_t)(S.best[lane] >> 32));
-                visit_node(scene.nodes + (base + rel), o, idx, idy, idz, tmin, tmax, octinv, ng_x, ng_y, tg_x, tg_y);
-            }
+            const uint32_t base = ng_x;
+            uint32_t rest = ng_y;
+            const uint32_t rel = next_child(rest, octinv);
+            if (rest & 0xff000000u) { st.x[sp] = base; st.y[sp] = rest; sp++; }
+            if (COUNT) c_nodes++;
+            const float tmax = COOP ? __uint_as_float((uint32_t)(S.best[lane] >> 32)) : rec.t;
+            visit_node(scene.nodes + (base + rel), o, idx, idy, idz, tmin, tmax, octinv, ng_x, ng_y, tg_x, tg_y);
         }
 
         __syncwarp();
-        if (!COOP) {   // comparison variant: every lane loops over its own primitives
-            if (tg_y) {
-                const vec3 rd = mk3(S.ray[3][lane], S.ray[4][lane], S.ray[5][lane]);
-                HitRec rec;
-                const unsigned long long b = S.best[lane];
-                rec.t = __uint_as_float((uint32_t)(b >> 32));
-                rec.id = (int32_t)(0xffffffffu - (uint32_t)b);
-                rec.prim = S.win[lane];
-                if (rec.prim == 0xffffffffu) rec.id = -1;
-                bool any = false;
-                while (tg_y) {
-                    const int i = 31 - __clz((int)tg_y);
-                    tg_y &= ~(1u << i);
-                    if (COUNT) c_prims++;
-                    any |= test_prim(scene.prims, tg_x + (uint32_t)i, o, rd, tmin, rec);
-                }
-                if (any) {
-                    S.best[lane] = ((unsigned long long)__float_as_uint(rec.t) << 32) | (unsigned long long)(0xffffffffu - (uint32_t)rec.id);
-                    S.win[lane] = rec.prim;
-                }
+        if (!COOP) {   // every lane loops over its own primitives; closest hit kept in registers
+            while (tg_y) {
+                const int i = 31 - __clz((int)tg_y);
+                tg_y &= ~(1u << i);
+                if (COUNT) c_prims++;
+                test_prim(scene.prims, tg_x + (uint32_t)i, o, d, tmin, rec);
             }
-            __syncwarp();
-            continue;
-        }
+        } else {
         // cooperative primitive rounds: pool the warp's (ray, primitive) pairs, one pair per lane
         while (true) {
             int cnt = __popc(tg_y);
@@ -340,6 +312,24 @@ __global__ void __launch_bounds__(256) k_wf_extend(SceneView scene, WfView w, co
                 __syncwarp();
                 if (hit && S.best[owner] == key) S.win[owner] = pi;
                 __syncwarp();
+            }
+        }
+        }
+        // end of the round: a lane whose node group is used up takes the next one from its stack, or is done
+        // (done lanes are refilled at the top of the loop, so they do not sit through another round)
+        if (has_ray && (ng_y & 0xff000000u) == 0u) {
+            if (sp == 0) {
+                float t;
+                uint32_t win;
+                if (COOP) { win = S.win[lane]; t = __uint_as_float((uint32_t)(S.best[lane] >> 32)); }
+                else { win = rec.id >= 0 ? rec.prim : 0xffffffffu; t = rec.t; }
+                float2* c = reinterpret_cast<float2*>(&w.C[pix]);
+                *c = make_float2(win != 0xffffffffu ? t : -1.f, __uint_as_float(win));
+                has_ray = false;
+            } else {
+                sp--;
+                ng_x = st.x[sp];
+                ng_y = st.y[sp];
             }
         }
     }
