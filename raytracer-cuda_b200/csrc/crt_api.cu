@@ -72,6 +72,7 @@ static SceneView scene_view(const crt_ctx* ctx) {
     SceneView v;
     v.nodes = ctx->bvh.nodes; v.prims = ctx->bvh.prims; v.mats = ctx->d_mats;
     v.num_mats = ctx->num_mats; v.num_nodes = ctx->bvh.num_nodes; v.num_prims = ctx->bvh.num_prims;
+    v.giant_base = ctx->bvh.giant_base; v.giant_count = ctx->bvh.giant_count;
     return v;
 }
 

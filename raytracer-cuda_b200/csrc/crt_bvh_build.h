@@ -26,10 +26,12 @@ namespace crt {
 CRT_HD uint32_t atomic_add_u32(uint32_t* p, uint32_t v) { return atomicAdd(p, v); }
 CRT_HD void atomic_min_i32(int32_t* p, int32_t v) { atomicMin(p, v); }
 CRT_HD void atomic_max_i32(int32_t* p, int32_t v) { atomicMax(p, v); }
+CRT_HD void atomic_max_u64(unsigned long long* p, unsigned long long v) { atomicMax(p, v); }
 #else
 CRT_HD uint32_t atomic_add_u32(uint32_t* p, uint32_t v) { uint32_t o = *p; *p = o + v; return o; }
 CRT_HD void atomic_min_i32(int32_t* p, int32_t v) { if (v < *p) *p = v; }
 CRT_HD void atomic_max_i32(int32_t* p, int32_t v) { if (v > *p) *p = v; }
+CRT_HD void atomic_max_u64(unsigned long long* p, unsigned long long v) { if (v > *p) *p = v; }
 #endif
 
 // order-preserving float <-> int32 (for atomic min/max on floats)
@@ -58,7 +60,6 @@ struct PrimBoxFn {
     SceneInput in;
     f4* plo;            // per primitive (lo.xyz, -)
     f4* phi;            // per primitive (hi.xyz, -)
-    int32_t* cbounds;   // centroid bounds, float_ordered: min xyz, max xyz
     CRT_HD void operator()(int i) const {
         float lx, ly, lz, hx, hy, hz;
         if ((uint32_t)i < in.num_triangles) {
@@ -80,7 +81,71 @@ struct PrimBoxFn {
         f4 hi; hi.x = hx; hi.y = hy; hi.z = hz; hi.w = 0.f;
         plo[i] = lo;
         phi[i] = hi;
-        const float mx = 0.5f * (lx + hx), my = 0.5f * (ly + hy), mz = 0.5f * (lz + hz);
+    }
+};
+
+// ---- step 1b: giant primitives ------------------------------------------------------------------
+// A primitive that dwarfs everything else (the reference always adds a ground sphere of radius 999 under a
+// scene of extent 0.6, CUDAKernels.h:69) would be the root's sibling of "all the rest": every ray pays one
+// wide-node visit just to step past it, and its centroid stretches the Morton grid. Up to CRT_MAX_GIANTS such
+// primitives are taken out of the BVH; every ray tests them directly before it traverses (trace_giants).
+#define CRT_MAX_GIANTS 4
+#define CRT_GIANT_RATIO 16.0f
+
+struct GiantSet {
+    uint32_t count;
+    uint32_t id[CRT_MAX_GIANTS];   // ascending
+    CRT_HD bool has(uint32_t p) const {
+        for (uint32_t k = 0; k < count; k++) if (id[k] == p) return true;
+        return false;
+    }
+    // j-th primitive that is not a giant
+    CRT_HD uint32_t remap(uint32_t j) const {
+        uint32_t p = j;
+        for (uint32_t k = 0; k < count; k++) if (p >= id[k]) p++;
+        return p;
+    }
+};
+
+// largest primitive (by longest box side) outside `skip`: key = extent bits << 32 | prim
+struct GiantScanFn {
+    const f4* plo;
+    const f4* phi;
+    GiantSet skip;
+    unsigned long long* key;
+    CRT_HD void operator()(int i) const {
+        if (skip.has((uint32_t)i)) return;
+        const float e = fmaxf(phi[i].x - plo[i].x, fmaxf(phi[i].y - plo[i].y, phi[i].z - plo[i].z));
+        atomic_max_u64(key, ((unsigned long long)f_bits(e > 0.f ? e : 0.f) << 32) | (unsigned long long)(uint32_t)i);
+    }
+};
+
+// bounds of all primitive boxes outside `skip` (float_ordered min xyz, max xyz)
+struct RestBoundsFn {
+    const f4* plo;
+    const f4* phi;
+    GiantSet skip;
+    int32_t* bounds;
+    CRT_HD void operator()(int i) const {
+        if (skip.has((uint32_t)i)) return;
+        atomic_min_i32(&bounds[0], float_ordered(plo[i].x));
+        atomic_min_i32(&bounds[1], float_ordered(plo[i].y));
+        atomic_min_i32(&bounds[2], float_ordered(plo[i].z));
+        atomic_max_i32(&bounds[3], float_ordered(phi[i].x));
+        atomic_max_i32(&bounds[4], float_ordered(phi[i].y));
+        atomic_max_i32(&bounds[5], float_ordered(phi[i].z));
+    }
+};
+
+// centroid bounds of the primitives that stay in the BVH
+struct CentroidBoundsFn {
+    const f4* plo;
+    const f4* phi;
+    GiantSet giants;
+    int32_t* cbounds;   // centroid bounds, float_ordered: min xyz, max xyz
+    CRT_HD void operator()(int j) const {
+        const uint32_t p = giants.remap((uint32_t)j);
+        const float mx = 0.5f * (plo[p].x + phi[p].x), my = 0.5f * (plo[p].y + phi[p].y), mz = 0.5f * (plo[p].z + phi[p].z);
         atomic_min_i32(&cbounds[0], float_ordered(mx));
         atomic_min_i32(&cbounds[1], float_ordered(my));
         atomic_min_i32(&cbounds[2], float_ordered(mz));
@@ -88,6 +153,14 @@ struct PrimBoxFn {
         atomic_max_i32(&cbounds[4], float_ordered(my));
         atomic_max_i32(&cbounds[5], float_ordered(mz));
     }
+};
+
+struct GiantRecordsFn {   // primitive records of the giants, appended after the BVH's records
+    SceneInput in;
+    GiantSet giants;
+    PrimRec* prims;
+    uint32_t base;
+    CRT_HD void operator()(int k) const;
 };
 
 // ---- step 2: Morton codes -----------------------------------------------------------------
@@ -105,9 +178,11 @@ struct MortonFn {
     const f4* plo;
     const f4* phi;
     const int32_t* cbounds;
+    GiantSet giants;
     uint64_t* keys;
-    uint32_t* vals;
-    CRT_HD void operator()(int i) const {
+    uint32_t* vals;     // primitive number (scene numbering)
+    CRT_HD void operator()(int j) const {
+        const uint32_t i = giants.remap((uint32_t)j);
         const float bx = ordered_float(cbounds[0]), by = ordered_float(cbounds[1]), bz = ordered_float(cbounds[2]);
         const float ex = ordered_float(cbounds[3]) - bx, ey = ordered_float(cbounds[4]) - by, ez = ordered_float(cbounds[5]) - bz;
         const float mx = 0.5f * (plo[i].x + phi[i].x), my = 0.5f * (plo[i].y + phi[i].y), mz = 0.5f * (plo[i].z + phi[i].z);
@@ -116,8 +191,8 @@ struct MortonFn {
         const uint32_t qx = (uint32_t)fminf(fmaxf(nx * scale, 0.f), scale);
         const uint32_t qy = (uint32_t)fminf(fmaxf(ny * scale, 0.f), scale);
         const uint32_t qz = (uint32_t)fminf(fmaxf(nz * scale, 0.f), scale);
-        keys[i] = (spread21(qx) << 2) | (spread21(qy) << 1) | spread21(qz);
-        vals[i] = (uint32_t)i;
+        keys[j] = (spread21(qx) << 2) | (spread21(qy) << 1) | spread21(qz);
+        vals[j] = i;
     }
 };
 
@@ -266,6 +341,8 @@ CRT_HD PrimRec make_prim_record(const SceneInput& in, uint32_t p) {
     }
     return r;
 }
+
+CRT_HD void GiantRecordsFn::operator()(int k) const { prims[base + (uint32_t)k] = make_prim_record(in, giants.id[k]); }
 
 struct CollapseFn {
     const f4* blo;

@@ -19,7 +19,9 @@ struct WideBvh {
     WideNode* nodes = nullptr;   // exec memory, num_nodes entries (capacity node_capacity)
     PrimRec* prims = nullptr;    // exec memory, num_prims entries, leaf order
     uint32_t num_nodes = 0;
-    uint32_t num_prims = 0;
+    uint32_t num_prims = 0;      // all primitive records: the BVH's in leaf order, then the giants
+    uint32_t giant_base = 0;     // index of the first giant record (= primitives inside the BVH)
+    uint32_t giant_count = 0;    // primitives kept out of the BVH and tested by every ray (CRT_MAX_GIANTS)
     uint32_t depth = 0;          // wide levels
     uint32_t ploc_rounds = 0;
 };
@@ -27,41 +29,87 @@ struct WideBvh {
 // Returns 0 on success, CRT_E_* otherwise. `in` points into exec memory.
 template <class Exec>
 int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& out) {
-    const uint32_t N = in.num_triangles + in.num_spheres;
-    if (N == 0) return CRT_E_INVALID;
-    if (N > 0x3fffffffu) return CRT_E_LIMIT;
+    const uint32_t Nall = in.num_triangles + in.num_spheres;
+    if (Nall == 0) return CRT_E_INVALID;
+    if (Nall > 0x07ffffffu) return CRT_E_LIMIT;   // primitive record indices travel in 27 bits
     if (leaf_max < 1) leaf_max = 1;
     if (leaf_max > 3) leaf_max = 3;
-    const int n0 = (int)N;
+    const uint32_t N_alloc = Nall;
 
-    f4* plo = ex.template alloc<f4>(N);
-    f4* phi = ex.template alloc<f4>(N);
+    f4* plo = ex.template alloc<f4>(N_alloc);
+    f4* phi = ex.template alloc<f4>(N_alloc);
     int32_t* cbounds = ex.template alloc<int32_t>(6);
-    uint64_t* keys = ex.template alloc<uint64_t>(N);
-    uint64_t* keys_tmp = ex.template alloc<uint64_t>(N);
-    uint32_t* vals = ex.template alloc<uint32_t>(N);
-    uint32_t* vals_tmp = ex.template alloc<uint32_t>(N);
-    const size_t nb = (size_t)2 * N;   // 2N-1 binary nodes
+    uint64_t* keys = ex.template alloc<uint64_t>(N_alloc);
+    uint64_t* keys_tmp = ex.template alloc<uint64_t>(N_alloc);
+    uint32_t* vals = ex.template alloc<uint32_t>(N_alloc);
+    uint32_t* vals_tmp = ex.template alloc<uint32_t>(N_alloc);
+    const size_t nb = (size_t)2 * N_alloc;   // 2N-1 binary nodes
     f4* blo = ex.template alloc<f4>(nb);
     f4* bhi = ex.template alloc<f4>(nb);
     uint32_t* bcount = ex.template alloc<uint32_t>(nb);
-    uint32_t* cl_a = ex.template alloc<uint32_t>(N);
-    uint32_t* cl_b = ex.template alloc<uint32_t>(N);
-    uint32_t* nearest = ex.template alloc<uint32_t>(N);
-    uint32_t* merged = ex.template alloc<uint32_t>(N);
-    uint32_t* flags = ex.template alloc<uint32_t>(N);
-    uint32_t* pos = ex.template alloc<uint32_t>(N);
+    uint32_t* cl_a = ex.template alloc<uint32_t>(N_alloc);
+    uint32_t* cl_b = ex.template alloc<uint32_t>(N_alloc);
+    uint32_t* nearest = ex.template alloc<uint32_t>(N_alloc);
+    uint32_t* merged = ex.template alloc<uint32_t>(N_alloc);
+    uint32_t* flags = ex.template alloc<uint32_t>(N_alloc);
+    uint32_t* pos = ex.template alloc<uint32_t>(N_alloc);
     uint32_t* counters = ex.template alloc<uint32_t>(4);   // [0] wide nodes [1] prims [2] binary nodes [3] ploc total
     if (!plo || !phi || !cbounds || !keys || !keys_tmp || !vals || !vals_tmp || !blo || !bhi || !bcount || !cl_a || !cl_b ||
         !nearest || !merged || !flags || !pos || !counters)
         return CRT_E_NOMEM;
 
-    // 1. boxes + centroid bounds
+    // 1. boxes
+    {
+        PrimBoxFn f;
+        f.in = in; f.plo = plo; f.phi = phi;
+        ex.for_n((int)Nall, f);
+    }
+    // 1b. giants: repeatedly take out the largest primitive while it is CRT_GIANT_RATIO x larger than the
+    //     bounds of everything else
+    GiantSet giants;
+    giants.count = 0;
+    for (int k = 0; k < CRT_MAX_GIANTS; k++) giants.id[k] = 0xffffffffu;
+    {
+        unsigned long long* key = ex.template alloc<unsigned long long>(1);
+        if (!key) return CRT_E_NOMEM;
+        while (giants.count < CRT_MAX_GIANTS && Nall - giants.count >= 2) {
+            const unsigned long long zero = 0ull;
+            ex.upload(key, &zero, sizeof(zero));
+            GiantScanFn fs;
+            fs.plo = plo; fs.phi = phi; fs.skip = giants; fs.key = key;
+            ex.for_n((int)Nall, fs);
+            unsigned long long hk = 0ull;
+            ex.download(&hk, key, sizeof(hk));
+            const uint32_t cand = (uint32_t)(hk & 0xffffffffull);
+            const float cand_extent = bits_f((uint32_t)(hk >> 32));
+            GiantSet with = giants;
+            {   // insert keeping ids ascending
+                uint32_t pos = with.count;
+                while (pos > 0 && with.id[pos - 1] > cand) { with.id[pos] = with.id[pos - 1]; pos--; }
+                with.id[pos] = cand;
+                with.count++;
+            }
+            const int32_t init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int32_t)0x80000000, (int32_t)0x80000000, (int32_t)0x80000000};
+            ex.upload(cbounds, init, sizeof(init));
+            RestBoundsFn fr;
+            fr.plo = plo; fr.phi = phi; fr.skip = with; fr.bounds = cbounds;
+            ex.for_n((int)Nall, fr);
+            int32_t hb[6];
+            ex.download(hb, cbounds, sizeof(hb));
+            const float rest = fmaxf(ordered_float(hb[3]) - ordered_float(hb[0]),
+                                     fmaxf(ordered_float(hb[4]) - ordered_float(hb[1]), ordered_float(hb[5]) - ordered_float(hb[2])));
+            if (!(rest > 0.f) || !(cand_extent > CRT_GIANT_RATIO * rest)) break;
+            giants = with;
+        }
+        ex.release(key);
+    }
+    const uint32_t N = Nall - giants.count;   // primitives inside the BVH
+    const int n0 = (int)N;
     {
         const int32_t init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int32_t)0x80000000, (int32_t)0x80000000, (int32_t)0x80000000};
         ex.upload(cbounds, init, sizeof(init));
-        PrimBoxFn f;
-        f.in = in; f.plo = plo; f.phi = phi; f.cbounds = cbounds;
+        CentroidBoundsFn f;
+        f.plo = plo; f.phi = phi; f.giants = giants; f.cbounds = cbounds;
         ex.for_n(n0, f);
     }
     // 2. Morton order
@@ -69,7 +117,7 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
     uint32_t* vals_sorted = vals;
     {
         MortonFn f;
-        f.plo = plo; f.phi = phi; f.cbounds = cbounds; f.keys = keys; f.vals = vals;
+        f.plo = plo; f.phi = phi; f.cbounds = cbounds; f.giants = giants; f.keys = keys; f.vals = vals;
         ex.for_n(n0, f);
         ex.sort_pairs(keys, vals, keys_tmp, vals_tmp, n0, &keys_sorted, &vals_sorted);
     }
@@ -113,7 +161,7 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
     // was given its own frame, CollapseFn), of which there are 2N-1; N prim records.
     const uint32_t node_cap = 2 * N;
     out.nodes = ex.template alloc<WideNode>(node_cap);
-    out.prims = ex.template alloc<PrimRec>(N);
+    out.prims = ex.template alloc<PrimRec>(Nall);
     uint32_t* wide_bnode = ex.template alloc<uint32_t>(node_cap);
     if (!out.nodes || !out.prims || !wide_bnode) return CRT_E_NOMEM;
     ex.upload(wide_bnode, &root, sizeof(uint32_t));
@@ -141,6 +189,15 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
     ex.release(vals_tmp); ex.release(vals); ex.release(keys_tmp); ex.release(keys);
     ex.release(cbounds); ex.release(phi); ex.release(plo);
     if (out.num_prims != N) return CRT_E_CUDA;
+    // giants: records appended after the BVH's
+    out.giant_base = N;
+    out.giant_count = giants.count;
+    if (giants.count) {
+        GiantRecordsFn f;
+        f.in = in; f.giants = giants; f.prims = out.prims; f.base = N;
+        ex.for_n((int)giants.count, f);
+    }
+    out.num_prims = Nall;
     return CRT_OK;
 }
 

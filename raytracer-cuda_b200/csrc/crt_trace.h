@@ -262,12 +262,22 @@ struct Traverser {
     }
 };
 
+// Primitives kept out of the BVH (crt_bvh_build.h "giant primitives"): tested by every ray before it traverses.
+template <bool COUNT>
+CRT_HD void trace_giants(const SceneView& sc, vec3 o, vec3 d, float tmin, HitRec& rec, TraceCounters* ctr) {
+    for (uint32_t g = 0; g < sc.giant_count; g++) {
+        if (COUNT) ctr->prims++;
+        test_prim(sc.prims, sc.giant_base + g, o, d, tmin, rec);
+    }
+}
+
 // Closest hit in [tmin, tmax]. COUNT switches the work counters on (crt_render_counted).
 template <bool COUNT>
 CRT_HD bool trace_closest(const SceneView& sc, vec3 o, vec3 d, float tmin, float tmax, HitRec& rec, TraceCounters* ctr) {
     Traverser tr;
     TravStack st;
     tr.begin(o, d, tmin, tmax);
+    trace_giants<COUNT>(sc, o, d, tmin, tr.rec, ctr);
     while (!tr.step<COUNT>(sc, st, ctr)) {}
     rec = tr.rec;
     return rec.id >= 0;

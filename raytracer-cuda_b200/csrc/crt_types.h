@@ -59,6 +59,8 @@ struct SceneView {   // device pointers
     uint32_t num_mats;
     uint32_t num_nodes;
     uint32_t num_prims;
+    uint32_t giant_base;    // prims[giant_base .. giant_base+giant_count) are outside the BVH: every ray tests them
+    uint32_t giant_count;
 };
 
 struct RenderConst {

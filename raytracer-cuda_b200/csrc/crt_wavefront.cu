@@ -238,6 +238,15 @@ __global__ void __launch_bounds__(256) k_wf_extend(SceneView scene, WfView w, co
                     S.best[lane] = ((unsigned long long)0x7f800000u << 32) | 0xffffffffull;   // t = +inf
                     S.win[lane] = 0xffffffffu;
                 }
+                // primitives outside the BVH first: they bound the interval the traversal has to search
+                for (uint32_t g = 0; g < scene.giant_count; g++) {
+                    if (COUNT) c_prims++;
+                    test_prim(scene.prims, scene.giant_base + g, o, d, tmin, rec);
+                }
+                if (COOP && rec.id >= 0) {
+                    S.best[lane] = ((unsigned long long)__float_as_uint(rec.t) << 32) | (unsigned long long)(0xffffffffu - (uint32_t)rec.id);
+                    S.win[lane] = rec.prim;
+                }
                 has_ray = true;
                 c_rays++;
             }

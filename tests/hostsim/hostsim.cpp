@@ -54,6 +54,7 @@ hs_scene* hs_scene_create(const crt_scene* sc, int leaf_max) {
     for (uint32_t i = 0; i < sc->num_materials; i++) s->mats.push_back(make_mat_record(sc->materials[i]));
     s->view.nodes = s->bvh.nodes; s->view.prims = s->bvh.prims; s->view.mats = s->mats.data();
     s->view.num_mats = (uint32_t)s->mats.size(); s->view.num_nodes = s->bvh.num_nodes; s->view.num_prims = s->bvh.num_prims;
+    s->view.giant_base = s->bvh.giant_base; s->view.giant_count = s->bvh.giant_count;
     return s;
 }
 
@@ -62,6 +63,7 @@ void hs_scene_destroy(hs_scene* s) { if (s) { free(s->bvh.nodes); free(s->bvh.pr
 void hs_scene_info(const hs_scene* s, uint32_t out[4]) {
     out[0] = s->bvh.num_nodes; out[1] = s->bvh.num_prims; out[2] = s->bvh.depth; out[3] = s->bvh.ploc_rounds;
 }
+uint32_t hs_scene_giants(const hs_scene* s) { return s->bvh.giant_count; }
 
 const void* hs_scene_nodes(const hs_scene* s) { return s->bvh.nodes; }
 const void* hs_scene_prims(const hs_scene* s) { return s->bvh.prims; }
