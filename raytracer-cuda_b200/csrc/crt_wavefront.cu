@@ -190,8 +190,11 @@ struct WarpPool {
     uint32_t list[256];               // (owner lane << 27) | primitive record index
 };
 
+#ifndef CRT_EXTEND_MIN_BLOCKS
+#define CRT_EXTEND_MIN_BLOCKS 4
+#endif
 template <bool COUNT, bool COOP>
-__global__ void __launch_bounds__(256) k_wf_extend(SceneView scene, WfView w, const uint32_t* queue, uint32_t* qcount, int cur,
+__global__ void __launch_bounds__(256, CRT_EXTEND_MIN_BLOCKS) k_wf_extend(SceneView scene, WfView w, const uint32_t* queue, uint32_t* qcount, int cur,
                                                    unsigned long long* counters, int fetch_lanes, int postpone_lanes) {
     (void)postpone_lanes;
     __shared__ WarpPool pools[8];

@@ -1,7 +1,2 @@
-set -x
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
 P="python scripts/prof_render.py --reps 2 --spp 128"
-$P | grep -E "rep 1|bvh"
-CRT_COOP=1 $P | grep "rep 1"
-$P --mode megakernel | grep "rep 1"
-for s in spheres terrain; do python scripts/prof_render.py --reps 2 --spp 32 --scene $s | grep -E "rep 1|bvh"; done
+for v in b200 mb5 mb6 st24 mb5st24; do echo "LIB=$v"; CRT_LIB=$PWD/raytracer-cuda_b200/libcrt_$v.so $P | grep "rep 1"; done
