@@ -109,7 +109,9 @@ typedef struct crt_camera {
  * (reference: src/CUDARenderer.cuh:31-32, src/CUDAHelpers.h:28-35). */
 enum {
     CRT_MODE_WAVEFRONT  = 0,  /* raygen / extend / shade / accumulate kernels (default) */
-    CRT_MODE_MEGAKERNEL = 1   /* one thread per pixel, spp loop inside, for comparison  */
+    CRT_MODE_MEGAKERNEL = 1,  /* one thread per pixel, spp loop inside, for comparison  */
+    CRT_MODE_AUTO       = 2   /* wavefront for large frames over non-trivial scenes (>= 1.5 M pixels and
+                                 >= 4096 primitives), megakernel otherwise; same bits either way */
 };
 
 typedef struct crt_config {
@@ -166,7 +168,9 @@ typedef struct crt_stats {
     float    shade_ms;
     uint32_t extend_launches;
     uint32_t shade_launches;
-    uint64_t reserved[2];
+    uint32_t bvh_giants;       /* primitives kept out of the BVH and tested by every ray (<= 4)  */
+    uint32_t reserved32;
+    uint64_t reserved[1];
 } crt_stats;
 
 typedef struct crt_ctx crt_ctx;

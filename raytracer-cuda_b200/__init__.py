@@ -20,7 +20,7 @@ LIB_PATH = os.environ.get("CRT_LIB") or os.path.join(_HERE, "libcrt_b200.so")   
 CRT_OK = 0
 E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_IO, E_PARSE, E_LIMIT = -1, -2, -3, -4, -5, -6, -7
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT = 0, 1, 2, 3
-MODE_WAVEFRONT, MODE_MEGAKERNEL = 0, 1
+MODE_WAVEFRONT, MODE_MEGAKERNEL, MODE_AUTO = 0, 1, 2
 RENDER_ACCUMULATE, RENDER_NO_TONEMAP, RENDER_TIME_KERNELS = 1, 2, 4
 REFERENCE_SEED = 1804289383  # glibc rand() first value = what CUDARenderer::initialize passes (CUDARenderer.cuh:46)
 
@@ -62,7 +62,8 @@ class Stats(C.Structure):
                 ("scene_upload_ms", C.c_float), ("bvh_nodes", C.c_uint32), ("bvh_prims", C.c_uint32),
                 ("bvh_depth", C.c_uint32), ("kernel_launches", C.c_uint32),
                 ("nodes_fetched", C.c_uint64), ("prims_tested", C.c_uint64), ("extend_ms", C.c_float), ("shade_ms", C.c_float),
-                ("extend_launches", C.c_uint32), ("shade_launches", C.c_uint32), ("reserved", C.c_uint64 * 2)]
+                ("extend_launches", C.c_uint32), ("shade_launches", C.c_uint32), ("bvh_giants", C.c_uint32),
+                ("reserved32", C.c_uint32), ("reserved", C.c_uint64 * 1)]
 
 
 class CrtError(RuntimeError):

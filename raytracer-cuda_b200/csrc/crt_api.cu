@@ -97,7 +97,7 @@ int crt_create(crt_ctx** out_ctx, const crt_config* cfg) {
     *out_ctx = nullptr;
     if (cfg->width <= 0 || cfg->height <= 0 || (long long)cfg->width * cfg->height > (1ll << 30))
         return fail(nullptr, CRT_E_INVALID, "crt_create: bad image size");
-    if (cfg->mode != CRT_MODE_WAVEFRONT && cfg->mode != CRT_MODE_MEGAKERNEL) return fail(nullptr, CRT_E_INVALID, "crt_create: bad mode");
+    if (cfg->mode != CRT_MODE_WAVEFRONT && cfg->mode != CRT_MODE_MEGAKERNEL && cfg->mode != CRT_MODE_AUTO) return fail(nullptr, CRT_E_INVALID, "crt_create: bad mode");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev <= 0) { (void)cudaGetLastError(); return fail(nullptr, CRT_E_NO_DEVICE, "crt_create: no CUDA device (this library has no CPU fallback)"); }
@@ -122,7 +122,7 @@ int crt_create(crt_ctx** out_ctx, const crt_config* cfg) {
     if (e2 == cudaSuccess) e2 = cudaMalloc(&ctx->fb.counters, 8 * sizeof(unsigned long long));
     if (e2 == cudaSuccess) e2 = cudaMemsetAsync(ctx->fb.accum, 0, n * sizeof(float4), ctx->stream);
     if (e2 == cudaSuccess) e2 = cudaMemsetAsync(ctx->fb.rgba8, 0, n * sizeof(uint32_t), ctx->stream);
-    if (e2 == cudaSuccess && cfg->mode == CRT_MODE_WAVEFRONT) e2 = wavefront_create(&ctx->wf, cfg->width, cfg->height);
+    if (e2 == cudaSuccess && cfg->mode == CRT_MODE_WAVEFRONT) e2 = wavefront_create(&ctx->wf, cfg->width, cfg->height);   // AUTO: on first use
     if (e2 == cudaSuccess) e2 = cudaStreamSynchronize(ctx->stream);
     if (e2 != cudaSuccess) {
         int rc = fail_cuda(nullptr, e2, "crt_create: allocation");
@@ -213,6 +213,7 @@ int crt_set_scene(crt_ctx* ctx, const crt_scene* sc) {
     ctx->stats.bvh_nodes = ctx->bvh.num_nodes;
     ctx->stats.bvh_prims = ctx->bvh.num_prims;
     ctx->stats.bvh_depth = ctx->bvh.depth;
+    ctx->stats.bvh_giants = ctx->bvh.giant_count;
     ctx->scene_ready = true;
     return CRT_OK;
 }
@@ -239,11 +240,15 @@ static int render_impl(crt_ctx* ctx, const crt_render_params* p, bool counted) {
     a.rc.max_bounces = p->max_bounces; a.rc.min_bounces = p->min_bounces; a.rc.rr_max_prob = p->rr_max_prob;
     a.fb = ctx->fb;
     a.flags = p->flags;
+    bool mega = ctx->cfg.mode == CRT_MODE_MEGAKERNEL;
+    if (ctx->cfg.mode == CRT_MODE_AUTO)
+        mega = !((long long)ctx->cfg.width * ctx->cfg.height >= 1500000ll && ctx->bvh.num_prims >= 4096u);
+    if (!mega && !ctx->wf) CU(wavefront_create(&ctx->wf, ctx->cfg.width, ctx->cfg.height));
     CU(cudaMemsetAsync(ctx->fb.counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
     uint32_t launches = 0;
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
     KernelTimes kt;
-    if (ctx->cfg.mode == CRT_MODE_MEGAKERNEL) CU(launch_render_mega(a, counted, ctx->num_sms, ctx->stream, &launches));
+    if (mega) CU(launch_render_mega(a, counted, ctx->num_sms, ctx->stream, &launches));
     else CU(launch_render_wavefront(ctx->wf, a, counted, ctx->num_sms, ctx->stream, &launches, &kt));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     unsigned long long c[4] = {0, 0, 0, 0};
@@ -256,7 +261,7 @@ static int render_impl(crt_ctx* ctx, const crt_render_params* p, bool counted) {
     ctx->stats.nodes_fetched = c[2];
     ctx->stats.prims_tested = c[3];
     ctx->stats.kernel_launches = launches;
-    if (ctx->cfg.mode == CRT_MODE_MEGAKERNEL) { kt.extend_ms = ctx->stats.render_ms; kt.extend_launches = 1; }
+    if (mega) { kt.extend_ms = ctx->stats.render_ms; kt.extend_launches = 1; }
     ctx->stats.extend_ms = kt.extend_ms; ctx->stats.shade_ms = kt.shade_ms;
     ctx->stats.extend_launches = kt.extend_launches; ctx->stats.shade_launches = kt.shade_launches;
     return CRT_OK;

@@ -72,35 +72,39 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
     {
         unsigned long long* key = ex.template alloc<unsigned long long>(1);
         if (!key) return CRT_E_NOMEM;
-        while (giants.count < CRT_MAX_GIANTS && Nall - giants.count >= 2) {
+        // candidates: the CRT_MAX_GIANTS largest primitives, largest first; accept the longest prefix whose
+        // smallest member is still CRT_GIANT_RATIO x larger than the bounds of everything outside the prefix
+        GiantSet cand_set = giants, accepted = giants;
+        while (cand_set.count < CRT_MAX_GIANTS && Nall - cand_set.count >= 2) {
             const unsigned long long zero = 0ull;
             ex.upload(key, &zero, sizeof(zero));
             GiantScanFn fs;
-            fs.plo = plo; fs.phi = phi; fs.skip = giants; fs.key = key;
+            fs.plo = plo; fs.phi = phi; fs.skip = cand_set; fs.key = key;
             ex.for_n((int)Nall, fs);
             unsigned long long hk = 0ull;
             ex.download(&hk, key, sizeof(hk));
             const uint32_t cand = (uint32_t)(hk & 0xffffffffull);
             const float cand_extent = bits_f((uint32_t)(hk >> 32));
-            GiantSet with = giants;
             {   // insert keeping ids ascending
-                uint32_t pos = with.count;
-                while (pos > 0 && with.id[pos - 1] > cand) { with.id[pos] = with.id[pos - 1]; pos--; }
-                with.id[pos] = cand;
-                with.count++;
+                uint32_t pos = cand_set.count;
+                while (pos > 0 && cand_set.id[pos - 1] > cand) { cand_set.id[pos] = cand_set.id[pos - 1]; pos--; }
+                cand_set.id[pos] = cand;
+                cand_set.count++;
             }
             const int32_t init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int32_t)0x80000000, (int32_t)0x80000000, (int32_t)0x80000000};
             ex.upload(cbounds, init, sizeof(init));
             RestBoundsFn fr;
-            fr.plo = plo; fr.phi = phi; fr.skip = with; fr.bounds = cbounds;
+            fr.plo = plo; fr.phi = phi; fr.skip = cand_set; fr.bounds = cbounds;
             ex.for_n((int)Nall, fr);
             int32_t hb[6];
             ex.download(hb, cbounds, sizeof(hb));
             const float rest = fmaxf(ordered_float(hb[3]) - ordered_float(hb[0]),
                                      fmaxf(ordered_float(hb[4]) - ordered_float(hb[1]), ordered_float(hb[5]) - ordered_float(hb[2])));
-            if (!(rest > 0.f) || !(cand_extent > CRT_GIANT_RATIO * rest)) break;
-            giants = with;
+            if (!(rest > 0.f)) break;                                   // the rest is a point: keep it in a tree
+            if (cand_extent > CRT_GIANT_RATIO * rest) accepted = cand_set;
+            else if (!(cand_extent > rest)) break;                      // candidates no larger than the rest: no longer prefix can qualify
         }
+        giants = accepted;
         ex.release(key);
     }
     const uint32_t N = Nall - giants.count;   // primitives inside the BVH

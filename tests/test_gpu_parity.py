@@ -305,3 +305,96 @@ def test_empty_and_ragged_scenes(crt):
     assert np.array_equal((acc[..., :3] * np.float32(0.5)).view(np.uint32), orad.view(np.uint32))
     osc.close()
     r.close()
+
+
+def _small_camera(crt, pos=(0.0, 0.1, 2.5), vfov=40.0, aspect=1.0):
+    cam = crt.Camera()
+    cam.position[:] = pos
+    cam.world_up[:] = (0, 1, 0)
+    cam.yaw_deg, cam.pitch_deg, cam.vfov_deg, cam.aspect, cam.aperture, cam.focus_dist = -90, 0, vfov, aspect, 0.01, 2.5
+    return cam
+
+
+@pytest.mark.parametrize("W,H", [(37, 29), (1, 1), (130, 7)])
+def test_odd_image_sizes_all_modes_equal_oracle(crt, W, H):
+    """Sizes that are not multiples of the 16x16 tiles / of a warp; wavefront, megakernel and auto give the same bits."""
+    sc = crt.builtin_scene("cornell")
+    osc = ol.OracleScene(sc.pointer())
+    cam = sc.camera
+    cam.aspect = W / H
+    orad, oimg, orays = osc.render(cam, W, H, 3, 8, SEED)
+    for mode in (crt.MODE_WAVEFRONT, crt.MODE_MEGAKERNEL, crt.MODE_AUTO):
+        r = crt.Renderer(W, H, mode=mode)
+        r.set_scene(sc)
+        r.update_camera(cam)
+        r.initialize(SEED, 0)
+        st = r.render(3, 8)
+        rad = r.accum()[..., :3] / np.float32(3)
+        assert np.array_equal(r.image_rgba8(), oimg)
+        assert (np.abs(rad - orad) <= 1e-4 * np.maximum(np.abs(orad), 1e-3)).all()
+        assert int(st.rays) == int(orays)
+        r.close()
+    osc.close()
+    sc.free()
+
+
+def test_giant_primitives_and_degenerate_triangles(crt):
+    """Two huge spheres (ground + sky dome piece) next to a small mesh with a zero-area and a sliver triangle:
+    the giants leave the BVH (stats.bvh_giants), results stay the oracle's bit for bit."""
+    import ctypes as C
+    rs = np.random.RandomState(5)
+    pos = (rs.rand(60, 3).astype(np.float32) - 0.5) * 0.6
+    idx = rs.randint(0, 60, size=(40, 3)).astype(np.uint32)
+    idx[0] = (3, 3, 3)                 # zero-area triangle
+    idx[1] = (4, 5, 4)                 # degenerate (two equal vertices)
+    pos[7] = pos[8] + np.float32(1e-7)
+    idx[2] = (7, 8, 9)                 # sliver
+    tri_mat = rs.randint(0, 4, size=40).astype(np.int32)
+    spheres = [[0, -1000.3, 0, 1000.0], [0, 0.1, 0, 0.12], [900.0, 900.0, -900.0, 700.0]]
+    sph_mat = [0, 2, 1]
+    mats = [(crt.MAT_LAMBERTIAN, (0.5, 0.5, 0.5), (0, 0, 0), 0.0, 1.0), (crt.MAT_METAL, (0.8, 0.6, 0.2), (0, 0, 0), 0.3, 1.0),
+            (crt.MAT_DIELECTRIC, (1, 1, 1), (0, 0, 0), 0.0, 1.5), (crt.MAT_DIFFUSE_LIGHT, (0, 0, 0), (4, 4, 4), 0.0, 1.0)]
+    s, keep = crt.make_scene_struct(pos, idx, tri_mat, spheres, sph_mat, mats, mesh_tri_offset=[0, 40])
+    cam = _small_camera(crt)
+    W, H = 96, 64
+    cam.aspect = W / H
+    osc = ol.OracleScene(C.pointer(s))
+    orad, oimg, orays = osc.render(cam, W, H, 4, 12, SEED)
+    oid, ot = osc.primary(cam, W, H, SEED)
+    for mode in (crt.MODE_WAVEFRONT, crt.MODE_MEGAKERNEL):
+        r = crt.Renderer(W, H, mode=mode)
+        r.set_scene(s)
+        assert r.stats().bvh_giants == 2 and r.stats().bvh_prims == 43
+        r.update_camera(cam)
+        r.initialize(SEED, 0)
+        ids, t = r.primary_ids(SEED, 0)
+        assert np.array_equal(ids, oid) and np.array_equal(t.view(np.uint32), ot.view(np.uint32))
+        st = r.render(4, 12)
+        rad = r.accum()[..., :3] * np.float32(0.25)
+        exact = (rad.view(np.uint32) == orad.view(np.uint32)).all(axis=-1)
+        assert exact.mean() > 0.995, exact.mean()
+        assert (np.abs(rad - orad) <= 1e-4 * np.maximum(np.abs(orad), 1e-3)).all(axis=-1).mean() > 0.999
+        assert abs(int(st.rays) - int(orays)) <= 16
+        r.close()
+    osc.close()
+
+
+def test_second_set_scene_replaces_the_first(crt):
+    a, b = crt.builtin_scene("cornell"), crt.builtin_scene("spheres")
+    r = crt.Renderer(64, 48)
+    r.set_scene(a)
+    r.update_camera(a.camera)
+    r.initialize(SEED, 0)
+    r.render(2, 8)
+    r.set_scene(b)
+    r.update_camera(b.camera)
+    r.initialize(SEED, 0)
+    r.render(2, 20)
+    osc = ol.OracleScene(b.pointer())
+    orad, oimg, _ = osc.render(b.camera, 64, 48, 2, 20, SEED)
+    assert (r.image_rgba8() != oimg).any(axis=-1).mean() < 1e-3
+    assert r.stats().bvh_giants == 1             # the r=1000 ground sphere of the spheres scene
+    osc.close()
+    r.close()
+    a.free()
+    b.free()
