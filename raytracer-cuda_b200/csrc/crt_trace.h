@@ -44,13 +44,31 @@ CRT_HD u4 ld_u4(const u4* p) { return *p; }
 #endif
 
 CRT_HD float byte_f(uint32_t w, int i) { return (float)((w >> (8 * i)) & 0xffu); }
+// 32768 + byte i of w, exactly, built with ONE byte permute instead of shift + mask + int-to-float:
+// 0x47000000 is 32768.0f and mantissa bit 8 weighs 1.0 at that exponent, so dropping the byte into bits 8..15
+// adds it. The child-box bounds are then t = f*s + (o - 32768*s); the extra rounding of (o - 32768*s) is at
+// most 2^-9 |s| (1/512 of a grid step) and is covered by the conservative pad in visit_node.
+#define CRT_BYTE_MAGIC 32768.0f
+#if defined(__CUDA_ARCH__)
+CRT_HD float byte_magic(uint32_t w, int i) { return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7504u | ((uint32_t)i << 4))); }
+#else
+CRT_HD float byte_magic(uint32_t w, int i) { return bits_f(0x47000000u | (((w >> (8 * i)) & 0xffu) << 8)); }
+#endif
 
 // Primitive test against the interval [tmin, tmax] (both inclusive, Mesh.cuh:293 / Interval.cuh:33-35).
 // Returns the hit parameter and the caller's primitive id; no tie rule here.
-CRT_HD bool prim_hit(const PrimRec* prims, uint32_t index, vec3 o, vec3 d, float tmin, float tmax, float& t_out, int32_t& id_out) {
-    const f4 q0 = ld_f4(&prims[index].q0);
-    const f4 q1 = ld_f4(&prims[index].q1);
-    const f4 q2 = ld_f4(&prims[index].q2);
+struct PrimLoad {   // the three 16-byte loads of a primitive record, issued before the arithmetic that needs them
+    f4 q0, q1, q2;
+};
+CRT_HD PrimLoad load_prim(const PrimRec* prims, uint32_t index) {
+    PrimLoad r;
+    r.q0 = ld_f4(&prims[index].q0);
+    r.q1 = ld_f4(&prims[index].q1);
+    r.q2 = ld_f4(&prims[index].q2);
+    return r;
+}
+CRT_HD bool prim_hit_loaded(const PrimLoad& pr, vec3 o, vec3 d, float tmin, float tmax, float& t_out, int32_t& id_out) {
+    const f4 q0 = pr.q0, q1 = pr.q1, q2 = pr.q2;
     float t;
     if (f_bits(q2.w) == (uint32_t)PRIM_TRIANGLE) {
         // Mesh::rayTriangleIntersect, Mesh.cuh:266-293
@@ -89,6 +107,22 @@ CRT_HD bool prim_hit(const PrimRec* prims, uint32_t index, vec3 o, vec3 d, float
     return true;
 }
 
+CRT_HD bool prim_hit(const PrimRec* prims, uint32_t index, vec3 o, vec3 d, float tmin, float tmax, float& t_out, int32_t& id_out) {
+    return prim_hit_loaded(load_prim(prims, index), o, d, tmin, tmax, t_out, id_out);
+}
+
+// Acceptance rule on an already loaded record (see test_prim).
+CRT_HD bool test_prim_loaded(const PrimLoad& pr, uint32_t index, vec3 o, vec3 d, float tmin, HitRec& rec) {
+    float t;
+    int32_t id;
+    if (!prim_hit_loaded(pr, o, d, tmin, rec.t, t, id)) return false;
+    if (t == rec.t && id < rec.id) return false;
+    rec.t = t;
+    rec.prim = index;
+    rec.id = id;
+    return true;
+}
+
 // Sequential form: returns true when `rec` accepts the hit and updates rec.
 CRT_HD bool test_prim(const PrimRec* prims, uint32_t index, vec3 o, vec3 d, float tmin, HitRec& rec) {
     float t;
@@ -120,14 +154,14 @@ CRT_HD void visit_node(const WideNode* node, vec3 o, float idx, float idy, float
     const float sy = bits_f(((ew >> 8) & 0xffu) << 23) * idy;
     const float sz = bits_f(((ew >> 16) & 0xffu) << 23) * idz;
     const float ox = (px - o.x) * idx, oy = (py - o.y) * idy, oz = (pz - o.z) * idz;
-    // conservative slack: covers the rounding of (p-o)*idir and of the per-child fma
+    // conservative slack: covers the rounding of (p-o)*idir, of the per-child fma and of the magic-number shift
     const float eps = 4.76837158203125e-07f;   // 2^-21
-    const float padx = eps * (fabsf(ox) + 256.f * fabsf(sx));
-    const float pady = eps * (fabsf(oy) + 256.f * fabsf(sy));
-    const float padz = eps * (fabsf(oz) + 256.f * fabsf(sz));
-    const float oxn = ox - padx, oxf = ox + padx;
-    const float oyn = oy - pady, oyf = oy + pady;
-    const float ozn = oz - padz, ozf = oz + padz;
+    const float padx = eps * (fabsf(ox) + 256.f * fabsf(sx)) + 0.00390625f * fabsf(sx);
+    const float pady = eps * (fabsf(oy) + 256.f * fabsf(sy)) + 0.00390625f * fabsf(sy);
+    const float padz = eps * (fabsf(oz) + 256.f * fabsf(sz)) + 0.00390625f * fabsf(sz);
+    const float oxn = (ox - padx) - CRT_BYTE_MAGIC * sx, oxf = (ox + padx) - CRT_BYTE_MAGIC * sx;
+    const float oyn = (oy - pady) - CRT_BYTE_MAGIC * sy, oyf = (oy + pady) - CRT_BYTE_MAGIC * sy;
+    const float ozn = (oz - padz) - CRT_BYTE_MAGIC * sz, ozf = (oz + padz) - CRT_BYTE_MAGIC * sz;
 
     uint32_t hitmask = 0u;
 #if defined(__CUDA_ARCH__)
@@ -148,9 +182,9 @@ CRT_HD void visit_node(const WideNode* node, vec3 o, float idx, float idy, float
 #pragma unroll
 #endif
         for (int j = 0; j < 4; j++) {
-            const float t0x = byte_f(nearx, j) * sx + oxn, t1x = byte_f(farx, j) * sx + oxf;
-            const float t0y = byte_f(neary, j) * sy + oyn, t1y = byte_f(fary, j) * sy + oyf;
-            const float t0z = byte_f(nearz, j) * sz + ozn, t1z = byte_f(farz, j) * sz + ozf;
+            const float t0x = byte_magic(nearx, j) * sx + oxn, t1x = byte_magic(farx, j) * sx + oxf;
+            const float t0y = byte_magic(neary, j) * sy + oyn, t1y = byte_magic(fary, j) * sy + oyf;
+            const float t0z = byte_magic(nearz, j) * sz + ozn, t1z = byte_magic(farz, j) * sz + ozf;
             const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
             const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
             if (cmin <= cmax) {
@@ -243,13 +277,21 @@ struct Traverser {
                 break;
             }
 #endif
-            const int i = hi_bit(tg_y);
-            tg_y &= ~(1u << i);
-            if (COUNT) ctr->prims++;
+            // two records per trip: both loads in flight before the first test needs its data
+            const int i0 = hi_bit(tg_y);
+            tg_y &= ~(1u << i0);
+            const bool two = tg_y != 0u;
+            const int i1 = two ? hi_bit(tg_y) : i0;
+            tg_y &= ~(1u << i1);
+            const PrimLoad r0 = load_prim(sc.prims, tg_x + (uint32_t)i0);
+            const PrimLoad r1 = load_prim(sc.prims, tg_x + (uint32_t)i1);
+            if (COUNT) ctr->prims += two ? 2u : 1u;
 #ifdef CRT_PRIM_HOOK
-            CRT_PRIM_HOOK(tg_x + (uint32_t)i);
+            CRT_PRIM_HOOK(tg_x + (uint32_t)i0);
+            if (two) CRT_PRIM_HOOK(tg_x + (uint32_t)i1);
 #endif
-            test_prim(sc.prims, tg_x + (uint32_t)i, o, d, tmin, rec);
+            test_prim_loaded(r0, tg_x + (uint32_t)i0, o, d, tmin, rec);
+            if (two) test_prim_loaded(r1, tg_x + (uint32_t)i1, o, d, tmin, rec);
         }
 
         if ((ng_y & 0xff000000u) == 0u) {

@@ -37,7 +37,7 @@ struct WavefrontState {
     uint32_t* h_qcount = nullptr;   // pinned
     size_t n = 0;
     int blocks_extend = 0, blocks_shade = 0;
-    int fetch_lanes = CRT_FETCH_LANES, postpone_lanes = CRT_POSTPONE_LANES, coop = 0;   // tuning knobs (env CRT_FETCH_LANES / CRT_POSTPONE_LANES)
+    int fetch_lanes = CRT_FETCH_LANES, postpone_lanes = CRT_POSTPONE_LANES, coop = 0, shade_persistent = 1;   // tuning knobs (env CRT_FETCH_LANES / CRT_POSTPONE_LANES)
     cudaEvent_t ev[3 * 16 + 2] = {};   // CRT_RENDER_TIME_KERNELS: begin pair + 3 events per iteration of a batch
 };
 
@@ -274,11 +274,19 @@ __global__ void __launch_bounds__(256, CRT_EXTEND_MIN_BLOCKS) k_wf_extend(SceneV
 
         __syncwarp();
         if (!COOP) {   // every lane loops over its own primitives; closest hit kept in registers
+            // two records per trip: both loads are in flight before the first test needs its data (leaves of
+            // the wall quads hold triangle pairs), which halves the exposed L1/L2 latency of this phase
             while (tg_y) {
-                const int i = 31 - __clz((int)tg_y);
-                tg_y &= ~(1u << i);
-                if (COUNT) c_prims++;
-                test_prim(scene.prims, tg_x + (uint32_t)i, o, d, tmin, rec);
+                const int i0 = 31 - __clz((int)tg_y);
+                tg_y &= ~(1u << i0);
+                const bool two = tg_y != 0u;
+                const int i1 = two ? 31 - __clz((int)tg_y) : i0;
+                tg_y &= ~(1u << i1);
+                const PrimLoad r0 = load_prim(scene.prims, tg_x + (uint32_t)i0);
+                const PrimLoad r1 = load_prim(scene.prims, tg_x + (uint32_t)i1);
+                if (COUNT) c_prims += two ? 2u : 1u;
+                test_prim_loaded(r0, tg_x + (uint32_t)i0, o, d, tmin, rec);
+                if (two) test_prim_loaded(r1, tg_x + (uint32_t)i1, o, d, tmin, rec);
             }
         } else {
         // cooperative primitive rounds: pool the warp's (ray, primitive) pairs, one pair per lane
@@ -456,6 +464,7 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade, 256, 0);
     if (const char* v = getenv("CRT_FETCH_LANES")) s->fetch_lanes = atoi(v);
     if (const char* v = getenv("CRT_COOP")) s->coop = atoi(v);
+    if (const char* v = getenv("CRT_SHADE_PERSISTENT")) s->shade_persistent = atoi(v);
     if (const char* v = getenv("CRT_POSTPONE_LANES")) s->postpone_lanes = atoi(v);
     if (s->fetch_lanes < 1) s->fetch_lanes = 1;
     if (s->fetch_lanes > 32) s->fetch_lanes = 32;
@@ -493,18 +502,21 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
     if (timed) cudaEventRecord(ws->ev[3 * batch + 1], stream);
     nl++;
     int cur = 0;
+    uint32_t live = (uint32_t)ws->n;   // queue length of the current batch (host copy)
     const long long max_iters = (long long)a.rc.spp * a.rc.max_bounces + 1;
     long long it = 0;
     bool first = true;
     e = cudaGetLastError();
     while (e == cudaSuccess && it < max_iters) {
+        // shade: one CTA per 256 queue entries (CRT_SHADE_PERSISTENT=1: grid-stride over 148 x occupancy CTAs)
+        const int shade_grid = ws->shade_persistent ? grid_s : (int)((live + 255u) / 256u > 0 ? (live + 255u) / 256u : 1u);
         for (int b = 0; b < batch; b++) {
             if (timed) cudaEventRecord(ws->ev[3 * b], stream);
             if (counted) k_wf_extend<true, true><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
             else if (ws->coop) k_wf_extend<false, true><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
             else k_wf_extend<false, false><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
             if (timed) cudaEventRecord(ws->ev[3 * b + 1], stream);
-            k_wf_shade<<<grid_s, 256, 0, stream>>>(a, w, ws->queue[cur], ws->qcount, cur);
+            k_wf_shade<<<shade_grid, 256, 0, stream>>>(a, w, ws->queue[cur], ws->qcount, cur);
             if (timed) cudaEventRecord(ws->ev[3 * b + 2], stream);
             nl += 2;
             it++;
@@ -532,7 +544,8 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
             times->extend_launches += batch;
             times->shade_launches += batch;
         }
-        if (e == cudaSuccess && ws->h_qcount[cur] == 0u) break;
+        if (e == cudaSuccess) live = ws->h_qcount[cur];
+        if (e == cudaSuccess && live == 0u) break;
     }
     if (launches) *launches += nl;
     return e;
