@@ -363,7 +363,10 @@ __global__ void __launch_bounds__(256, CRT_EXTEND_MIN_BLOCKS) k_wf_extend(SceneV
 }
 
 // ---- shade: consume the hit, continue / finish / regenerate, Russian roulette, compact -----------------
-__global__ void __launch_bounds__(256) k_wf_shade(RenderArgs a, WfView w, uint32_t* queue, uint32_t* qcount, int cur) {
+#ifndef CRT_SHADE_MIN_BLOCKS
+#define CRT_SHADE_MIN_BLOCKS 5
+#endif
+__global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderArgs a, WfView w, uint32_t* queue, uint32_t* qcount, int cur) {
     const uint32_t count = qcount[cur];
     const uint32_t rounded = (count + 31u) & ~31u;
     const size_t n = (size_t)a.rc.width * a.rc.height;

@@ -1,4 +1,2 @@
-timeout 800 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
 P="python scripts/prof_render.py --reps 2 --spp 128"
-$P | grep "rep 1"; $P --mode megakernel | grep "rep 1"
-python scripts/prof_render.py --reps 2 --spp 32 --scene terrain | grep "rep 1"
+for v in b200 sb4 sb5 sb6 sb8; do echo "LIB=$v"; CRT_LIB=$PWD/raytracer-cuda_b200/libcrt_$v.so $P | grep "rep 1"; done
