@@ -27,14 +27,32 @@ namespace crt {
 #define CRT_FETCH_LANES 12
 #endif
 
-struct WavefrontState {
-    float4* A = nullptr;
-    float4* B = nullptr;
-    float4* C = nullptr;
+// The pixel set is split into CRT_WF_PARTS interleaved parts (2048-pixel tiles, round robin), each with its own
+// queue and its own extend -> shade chain on its own stream: while one part's extend kernel drains (its last,
+// longest rays run alone and latency bound: 16 % of the kernel's duration had idle SMs in ncu), the other
+// part's kernels fill the machine.
+#define CRT_WF_MAX_PARTS 2
+struct WfPart {
     uint32_t* queue[2] = {nullptr, nullptr};
     uint32_t* qcount = nullptr;     // [0],[1] queue sizes, [2] fetch cursor of extend
     uint32_t* tile_count = nullptr; // per-tile survivor counts / offsets of the compaction
     uint32_t* h_qcount = nullptr;   // pinned
+    uint32_t cap = 0;               // pixels of this part
+    uint32_t live = 0;              // queue length of the current batch (host copy)
+    int cur = 0;
+    bool done = false;
+    cudaStream_t stream = nullptr;  // part 0 runs on the caller's stream
+    cudaEvent_t ev_done = nullptr;
+};
+
+struct WavefrontState {
+    float4* A = nullptr;
+    float4* B = nullptr;
+    float4* C = nullptr;
+    WfPart part[CRT_WF_MAX_PARTS];
+    int parts = 2;   // env CRT_WF_PARTS
+    cudaStream_t side_stream = nullptr;
+    cudaEvent_t ev_fork = nullptr;
     size_t n = 0;
     int blocks_extend = 0, blocks_shade = 0;
     int fetch_lanes = CRT_FETCH_LANES, postpone_lanes = CRT_POSTPONE_LANES, coop = 0, shade_persistent = 1;   // tuning knobs (env CRT_FETCH_LANES / CRT_POSTPONE_LANES)
@@ -151,25 +169,33 @@ __global__ void __launch_bounds__(256) k_compact_scatter(const uint32_t* queue_i
 }
 
 // ---- begin: first camera ray of every pixel, queue = all pixels ---------------------------------
-__global__ void __launch_bounds__(256) k_wf_begin(RenderArgs a, WfView w, uint32_t* queue, uint32_t* qcount) {
+struct BeginQueues {
+    uint32_t* queue[CRT_WF_MAX_PARTS];
+    uint32_t* qcount[CRT_WF_MAX_PARTS];
+    uint32_t cap[CRT_WF_MAX_PARTS];
+    int parts;
+};
+__global__ void __launch_bounds__(256) k_wf_begin(RenderArgs a, WfView w, BeginQueues q) {
     const size_t n = (size_t)a.rc.width * a.rc.height;
-    const size_t rounded = (n + 31) & ~(size_t)31;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += (size_t)gridDim.x * blockDim.x) {
-        const bool valid = i < n;
-        if (valid) {
-            const int x = (int)(i % (size_t)a.rc.width), y = (int)(i / (size_t)a.rc.width);
-            Rng rng = wf_load_rng(a.fb.rng, n, i);
-            vec3 o, d;
-            camera_ray(a.cam, x, y, a.rc.width, a.rc.height, rng, o, d);
-            wf_store_rng(a.fb.rng, n, i, rng);
-            w.A[i] = make_float4(o.x, o.y, o.z, 1.f);
-            w.B[i] = make_float4(d.x, d.y, d.z, 1.f);
-            w.C[i] = make_float4(0.f, 0.f, 1.f, __uint_as_float(0u));
-            if (!(a.flags & CRT_RENDER_ACCUMULATE)) a.fb.accum[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            queue[i] = (uint32_t)i;
-        }
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const int x = (int)(i % (size_t)a.rc.width), y = (int)(i / (size_t)a.rc.width);
+        Rng rng = wf_load_rng(a.fb.rng, n, i);
+        vec3 o, d;
+        camera_ray(a.cam, x, y, a.rc.width, a.rc.height, rng, o, d);
+        wf_store_rng(a.fb.rng, n, i, rng);
+        w.A[i] = make_float4(o.x, o.y, o.z, 1.f);
+        w.B[i] = make_float4(d.x, d.y, d.z, 1.f);
+        w.C[i] = make_float4(0.f, 0.f, 1.f, __uint_as_float(0u));
+        if (!(a.flags & CRT_RENDER_ACCUMULATE)) a.fb.accum[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        // tile t of CRT_COMPACT_TILE pixels belongs to part t % parts; only the last tile can be partial
+        const size_t tile = i / CRT_COMPACT_TILE;
+        const int p = (int)(tile % (size_t)q.parts);
+        q.queue[p][(tile / (size_t)q.parts) * CRT_COMPACT_TILE + (i % CRT_COMPACT_TILE)] = (uint32_t)i;
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) { qcount[0] = (uint32_t)n; qcount[1] = 0u; qcount[2] = 0u; }
+    if (blockIdx.x == 0 && threadIdx.x < q.parts) {
+        uint32_t* c = q.qcount[threadIdx.x];
+        c[0] = q.cap[threadIdx.x]; c[1] = 0u; c[2] = 0u;
+    }
 }
 
 // ---- extend: closest hit for every queued ray -------------------------------------------------------
@@ -190,15 +216,18 @@ struct WarpPool {
     uint32_t list[256];               // (owner lane << 27) | primitive record index
 };
 
+#ifndef CRT_EXTEND_THREADS
+#define CRT_EXTEND_THREADS 256
+#endif
 #ifndef CRT_EXTEND_MIN_BLOCKS
-#define CRT_EXTEND_MIN_BLOCKS 4
+#define CRT_EXTEND_MIN_BLOCKS (1024 / CRT_EXTEND_THREADS)
 #endif
 template <bool COUNT, bool COOP>
-__global__ void __launch_bounds__(256, CRT_EXTEND_MIN_BLOCKS) k_wf_extend(SceneView scene, WfView w, const uint32_t* queue, uint32_t* qcount, int cur,
+__global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_wf_extend(SceneView scene, WfView w, const uint32_t* queue, uint32_t* qcount, int cur,
                                                    unsigned long long* counters, int fetch_lanes, int postpone_lanes) {
     (void)postpone_lanes;
-    __shared__ WarpPool pools[8];
-    WarpPool& S = pools[threadIdx.x >> 5];
+    __shared__ WarpPool pools[COOP ? CRT_EXTEND_THREADS / 32 : 1];
+    WarpPool& S = pools[COOP ? threadIdx.x >> 5 : 0];
     const uint32_t count = qcount[cur];
     const int lane = threadIdx.x & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
@@ -454,16 +483,28 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
 cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
     WavefrontState* s = new WavefrontState();
     s->n = (size_t)width * height;
+    if (const char* v = getenv("CRT_WF_PARTS")) s->parts = atoi(v);
+    if (s->parts < 1) s->parts = 1;
+    if (s->parts > CRT_WF_MAX_PARTS) s->parts = CRT_WF_MAX_PARTS;
     cudaError_t e = cudaMalloc(&s->A, s->n * sizeof(float4));
     if (e == cudaSuccess) e = cudaMalloc(&s->B, s->n * sizeof(float4));
     if (e == cudaSuccess) e = cudaMalloc(&s->C, s->n * sizeof(float4));
-    if (e == cudaSuccess) e = cudaMalloc(&s->queue[0], s->n * sizeof(uint32_t));
-    if (e == cudaSuccess) e = cudaMalloc(&s->queue[1], s->n * sizeof(uint32_t));
-    if (e == cudaSuccess) e = cudaMalloc(&s->qcount, 4 * sizeof(uint32_t));
-    if (e == cudaSuccess) e = cudaMalloc(&s->tile_count, ((s->n + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE + 1) * sizeof(uint32_t));
-    if (e == cudaSuccess) e = cudaMallocHost(&s->h_qcount, 4 * sizeof(uint32_t));
+    const size_t tiles = (s->n + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE;
+    for (int p = 0; p < s->parts && e == cudaSuccess; p++) {
+        WfPart& q = s->part[p];
+        // part 0 can hold every pixel (a timed render runs as one part), the others their share of the tiles
+        const size_t cap = p == 0 ? s->n : ((tiles + (size_t)s->parts - 1) / (size_t)s->parts) * CRT_COMPACT_TILE;
+        e = cudaMalloc(&q.queue[0], cap * sizeof(uint32_t));
+        if (e == cudaSuccess) e = cudaMalloc(&q.queue[1], cap * sizeof(uint32_t));
+        if (e == cudaSuccess) e = cudaMalloc(&q.qcount, 4 * sizeof(uint32_t));
+        if (e == cudaSuccess) e = cudaMalloc(&q.tile_count, (tiles + 1) * sizeof(uint32_t));
+        if (e == cudaSuccess) e = cudaMallocHost(&q.h_qcount, 4 * sizeof(uint32_t));
+        if (e == cudaSuccess && p > 0) e = cudaEventCreateWithFlags(&q.ev_done, cudaEventDisableTiming);
+    }
+    if (e == cudaSuccess && s->parts > 1) e = cudaStreamCreateWithFlags(&s->side_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess && s->parts > 1) e = cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming);
     int be = 0, bs = 0;
-    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&be, k_wf_extend<false, true>, 256, 0);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&be, k_wf_extend<false, false>, CRT_EXTEND_THREADS, 0);
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade, 256, 0);
     if (const char* v = getenv("CRT_FETCH_LANES")) s->fetch_lanes = atoi(v);
     if (const char* v = getenv("CRT_COOP")) s->coop = atoi(v);
@@ -481,8 +522,14 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
 
 void wavefront_destroy(WavefrontState* s) {
     if (!s) return;
-    cudaFree(s->A); cudaFree(s->B); cudaFree(s->C); cudaFree(s->queue[0]); cudaFree(s->queue[1]); cudaFree(s->qcount); cudaFree(s->tile_count);
-    if (s->h_qcount) cudaFreeHost(s->h_qcount);
+    cudaFree(s->A); cudaFree(s->B); cudaFree(s->C);
+    for (WfPart& q : s->part) {
+        cudaFree(q.queue[0]); cudaFree(q.queue[1]); cudaFree(q.qcount); cudaFree(q.tile_count);
+        if (q.h_qcount) cudaFreeHost(q.h_qcount);
+        if (q.ev_done) cudaEventDestroy(q.ev_done);
+    }
+    if (s->side_stream) cudaStreamDestroy(s->side_stream);
+    if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     for (cudaEvent_t ev : s->ev) if (ev) cudaEventDestroy(ev);
     delete s;
 }
@@ -499,44 +546,74 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
     if (timed && !ws->ev[0])
         for (int i = 0; i < 3 * batch + 2 && e == cudaSuccess; i++) e = cudaEventCreate(&ws->ev[i]);
     if (e != cudaSuccess) return e;
+    // per-kernel times only mean something when the kernels run one after the other: a timed render is one part
+    const int parts = timed ? 1 : ws->parts;
+    const size_t tiles_all = (ws->n + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE;
+    BeginQueues bq = {};
+    bq.parts = parts;
+    for (int p = 0; p < parts; p++) {
+        WfPart& q = ws->part[p];
+        const size_t my_tiles = (tiles_all + (size_t)parts - 1 - (size_t)p) / (size_t)parts;
+        size_t cap = my_tiles * CRT_COMPACT_TILE;
+        if (my_tiles > 0 && (tiles_all - 1) % (size_t)parts == (size_t)p) cap -= tiles_all * CRT_COMPACT_TILE - ws->n;   // the partial last tile
+        q.cap = (uint32_t)cap; q.live = q.cap; q.cur = 0; q.done = q.cap == 0u;
+        q.stream = p == 0 ? stream : ws->side_stream;
+        bq.queue[p] = q.queue[0]; bq.qcount[p] = q.qcount; bq.cap[p] = q.cap;
+    }
     uint32_t nl = 0;
     if (timed) cudaEventRecord(ws->ev[3 * batch], stream);
-    k_wf_begin<<<grid_s, 256, 0, stream>>>(a, w, ws->queue[0], ws->qcount);
+    k_wf_begin<<<grid_s, 256, 0, stream>>>(a, w, bq);
     if (timed) cudaEventRecord(ws->ev[3 * batch + 1], stream);
     nl++;
-    int cur = 0;
-    uint32_t live = (uint32_t)ws->n;   // queue length of the current batch (host copy)
+    e = cudaGetLastError();
+    if (e == cudaSuccess && parts > 1) {
+        e = cudaEventRecord(ws->ev_fork, stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(ws->side_stream, ws->ev_fork, 0);
+    }
     const long long max_iters = (long long)a.rc.spp * a.rc.max_bounces + 1;
     long long it = 0;
     bool first = true;
-    e = cudaGetLastError();
     while (e == cudaSuccess && it < max_iters) {
-        // shade: one CTA per 256 queue entries (CRT_SHADE_PERSISTENT=1: grid-stride over 148 x occupancy CTAs)
-        const int shade_grid = ws->shade_persistent ? grid_s : (int)((live + 255u) / 256u > 0 ? (live + 255u) / 256u : 1u);
+        int active = 0;
         for (int b = 0; b < batch; b++) {
-            if (timed) cudaEventRecord(ws->ev[3 * b], stream);
-            if (counted) k_wf_extend<true, true><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
-            else if (ws->coop) k_wf_extend<false, true><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
-            else k_wf_extend<false, false><<<grid_e, 256, 0, stream>>>(a.scene, w, ws->queue[cur], ws->qcount, cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
-            if (timed) cudaEventRecord(ws->ev[3 * b + 1], stream);
-            k_wf_shade<<<shade_grid, 256, 0, stream>>>(a, w, ws->queue[cur], ws->qcount, cur);
-            if (timed) cudaEventRecord(ws->ev[3 * b + 2], stream);
-            nl += 2;
+            for (int p = 0; p < parts; p++) {
+                WfPart& q = ws->part[p];
+                if (q.done) continue;
+                cudaStream_t st = q.stream;
+                // shade: grid-stride over 148 x occupancy CTAs (CRT_SHADE_PERSISTENT=0: one CTA per 256 queue entries)
+                const int shade_grid = ws->shade_persistent ? grid_s : (int)((q.live + 255u) / 256u);
+                if (timed) cudaEventRecord(ws->ev[3 * b], st);
+                if (counted) k_wf_extend<true, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
+                else if (ws->coop) k_wf_extend<false, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
+                else k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
+                if (timed) cudaEventRecord(ws->ev[3 * b + 1], st);
+                k_wf_shade<<<shade_grid, 256, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur);
+                if (timed) cudaEventRecord(ws->ev[3 * b + 2], st);
+                nl += 2;
+            }
             it++;
         }
-        // order-preserving compaction of the survivors into the other queue
-        {
-            const int tiles = (int)((ws->n + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE);
-            k_compact_count<<<tiles, 256, 0, stream>>>(ws->queue[cur], ws->qcount, cur, ws->tile_count);
-            k_compact_scan<<<1, 1024, 0, stream>>>(ws->tile_count, tiles, ws->qcount, cur);
-            k_compact_scatter<<<tiles, 256, 0, stream>>>(ws->queue[cur], ws->queue[cur ^ 1], ws->qcount, cur, ws->tile_count);
+        // order-preserving compaction of the survivors into the other queue, then the new length comes back
+        for (int p = 0; p < parts; p++) {
+            WfPart& q = ws->part[p];
+            if (q.done) continue;
+            const int tiles = (int)((q.live + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE);
+            k_compact_count<<<tiles, 256, 0, q.stream>>>(q.queue[q.cur], q.qcount, q.cur, q.tile_count);
+            k_compact_scan<<<1, 1024, 0, q.stream>>>(q.tile_count, tiles, q.qcount, q.cur);
+            k_compact_scatter<<<tiles, 256, 0, q.stream>>>(q.queue[q.cur], q.queue[q.cur ^ 1], q.qcount, q.cur, q.tile_count);
             nl += 3;
-            cur ^= 1;
+            q.cur ^= 1;
+            cudaMemcpyAsync(q.h_qcount, q.qcount, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, q.stream);
         }
         e = cudaGetLastError();
-        if (e != cudaSuccess) break;
-        e = cudaMemcpyAsync(ws->h_qcount, ws->qcount, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+        for (int p = 0; p < parts && e == cudaSuccess; p++) {
+            WfPart& q = ws->part[p];
+            if (q.done) continue;
+            e = cudaStreamSynchronize(q.stream);
+            if (e != cudaSuccess) break;
+            q.live = q.h_qcount[q.cur];
+            if (q.live == 0u) q.done = true; else active++;
+        }
         if (e == cudaSuccess && timed) {
             float ms = 0.f;
             if (first) { cudaEventElapsedTime(&ms, ws->ev[3 * batch], ws->ev[3 * batch + 1]); times->shade_ms += ms; times->shade_launches++; first = false; }
@@ -547,9 +624,10 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
             times->extend_launches += batch;
             times->shade_launches += batch;
         }
-        if (e == cudaSuccess) live = ws->h_qcount[cur];
-        if (e == cudaSuccess && live == 0u) break;
+        if (active == 0) break;
     }
+    // every part's stream was synchronised by the host above, so work queued on `stream` after this call is ordered
+    // behind the side stream's kernels as well
     if (launches) *launches += nl;
     return e;
 }

@@ -1,3 +1,2 @@
-timeout 800 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
-P="python scripts/prof_render.py --reps 2 --spp 128"
-for c in 32 64 96 128 256 512; do echo "CHUNK=$c"; CRT_FETCH_CHUNK=$c $P | grep "rep 1"; done
+P="python scripts/prof_render.py --reps 3 --spp 128"
+for lib in b200 t128 t64; do for c in 1 2; do echo "LIB=$lib PARTS=$c"; CRT_LIB=/root/repo/raytracer-cuda_b200/libcrt_$lib.so CRT_WF_PARTS=$c $P | grep "rep [12]"; done; done
