@@ -31,7 +31,7 @@ namespace crt {
 // queue and its own extend -> shade chain on its own stream: while one part's extend kernel drains (its last,
 // longest rays run alone and latency bound: 16 % of the kernel's duration had idle SMs in ncu), the other
 // part's kernels fill the machine.
-#define CRT_WF_MAX_PARTS 2
+#define CRT_WF_MAX_PARTS 4
 struct WfPart {
     uint32_t* queue[2] = {nullptr, nullptr};
     uint32_t* qcount = nullptr;     // [0],[1] queue sizes, [2] fetch cursor of extend
@@ -51,12 +51,12 @@ struct WavefrontState {
     float4* C = nullptr;
     WfPart part[CRT_WF_MAX_PARTS];
     int parts = 2;   // env CRT_WF_PARTS
-    cudaStream_t side_stream = nullptr;
+    cudaStream_t side_stream[CRT_WF_MAX_PARTS] = {};   // [p] for part p >= 1
     cudaEvent_t ev_fork = nullptr;
     size_t n = 0;
     int blocks_extend = 0, blocks_shade = 0;
     int fetch_lanes = CRT_FETCH_LANES, postpone_lanes = CRT_POSTPONE_LANES, coop = 0, shade_persistent = 1;   // tuning knobs (env CRT_FETCH_LANES / CRT_POSTPONE_LANES)
-    cudaEvent_t ev[3 * 16 + 2] = {};   // CRT_RENDER_TIME_KERNELS: begin pair + 3 events per iteration of a batch
+    cudaEvent_t ev[3 * 16 * CRT_WF_MAX_PARTS + 2] = {};   // CRT_RENDER_TIME_KERNELS: begin pair + 3 events per (iteration, part) of a batch
 };
 
 struct WfView {
@@ -501,7 +501,7 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
         if (e == cudaSuccess) e = cudaMallocHost(&q.h_qcount, 4 * sizeof(uint32_t));
         if (e == cudaSuccess && p > 0) e = cudaEventCreateWithFlags(&q.ev_done, cudaEventDisableTiming);
     }
-    if (e == cudaSuccess && s->parts > 1) e = cudaStreamCreateWithFlags(&s->side_stream, cudaStreamNonBlocking);
+    for (int p = 1; p < s->parts && e == cudaSuccess; p++) e = cudaStreamCreateWithFlags(&s->side_stream[p], cudaStreamNonBlocking);
     if (e == cudaSuccess && s->parts > 1) e = cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming);
     int be = 0, bs = 0;
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&be, k_wf_extend<false, false>, CRT_EXTEND_THREADS, 0);
@@ -528,7 +528,7 @@ void wavefront_destroy(WavefrontState* s) {
         if (q.h_qcount) cudaFreeHost(q.h_qcount);
         if (q.ev_done) cudaEventDestroy(q.ev_done);
     }
-    if (s->side_stream) cudaStreamDestroy(s->side_stream);
+    for (cudaStream_t st : s->side_stream) if (st) cudaStreamDestroy(st);
     if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     for (cudaEvent_t ev : s->ev) if (ev) cudaEventDestroy(ev);
     delete s;
@@ -543,11 +543,11 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
     const int batch = 16;
     const bool timed = times != nullptr && (a.flags & CRT_RENDER_TIME_KERNELS);
     cudaError_t e = cudaSuccess;
+    const int parts = ws->parts;
+    const int ev_begin = 3 * batch * CRT_WF_MAX_PARTS;
     if (timed && !ws->ev[0])
-        for (int i = 0; i < 3 * batch + 2 && e == cudaSuccess; i++) e = cudaEventCreate(&ws->ev[i]);
+        for (int i = 0; i < ev_begin + 2 && e == cudaSuccess; i++) e = cudaEventCreate(&ws->ev[i]);
     if (e != cudaSuccess) return e;
-    // per-kernel times only mean something when the kernels run one after the other: a timed render is one part
-    const int parts = timed ? 1 : ws->parts;
     const size_t tiles_all = (ws->n + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE;
     BeginQueues bq = {};
     bq.parts = parts;
@@ -557,24 +557,28 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         size_t cap = my_tiles * CRT_COMPACT_TILE;
         if (my_tiles > 0 && (tiles_all - 1) % (size_t)parts == (size_t)p) cap -= tiles_all * CRT_COMPACT_TILE - ws->n;   // the partial last tile
         q.cap = (uint32_t)cap; q.live = q.cap; q.cur = 0; q.done = q.cap == 0u;
-        q.stream = p == 0 ? stream : ws->side_stream;
+        // per-kernel times only mean something when the kernels run one after the other: a timed render keeps
+        // the same launches (one per part) but puts them all on the caller's stream
+        q.stream = (p == 0 || timed) ? stream : ws->side_stream[p];
         bq.queue[p] = q.queue[0]; bq.qcount[p] = q.qcount; bq.cap[p] = q.cap;
     }
     uint32_t nl = 0;
-    if (timed) cudaEventRecord(ws->ev[3 * batch], stream);
+    if (timed) cudaEventRecord(ws->ev[ev_begin], stream);
     k_wf_begin<<<grid_s, 256, 0, stream>>>(a, w, bq);
-    if (timed) cudaEventRecord(ws->ev[3 * batch + 1], stream);
+    if (timed) cudaEventRecord(ws->ev[ev_begin + 1], stream);
     nl++;
     e = cudaGetLastError();
-    if (e == cudaSuccess && parts > 1) {
+    if (e == cudaSuccess && parts > 1 && !timed) {
         e = cudaEventRecord(ws->ev_fork, stream);
-        if (e == cudaSuccess) e = cudaStreamWaitEvent(ws->side_stream, ws->ev_fork, 0);
+        for (int p = 1; p < parts && e == cudaSuccess; p++) e = cudaStreamWaitEvent(ws->side_stream[p], ws->ev_fork, 0);
     }
     const long long max_iters = (long long)a.rc.spp * a.rc.max_bounces + 1;
     long long it = 0;
     bool first = true;
     while (e == cudaSuccess && it < max_iters) {
         int active = 0;
+        bool timed_part[CRT_WF_MAX_PARTS];
+        for (int p = 0; p < CRT_WF_MAX_PARTS; p++) timed_part[p] = p < parts && !ws->part[p].done;
         for (int b = 0; b < batch; b++) {
             for (int p = 0; p < parts; p++) {
                 WfPart& q = ws->part[p];
@@ -582,13 +586,13 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                 cudaStream_t st = q.stream;
                 // shade: grid-stride over 148 x occupancy CTAs (CRT_SHADE_PERSISTENT=0: one CTA per 256 queue entries)
                 const int shade_grid = ws->shade_persistent ? grid_s : (int)((q.live + 255u) / 256u);
-                if (timed) cudaEventRecord(ws->ev[3 * b], st);
+                if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p)], st);
                 if (counted) k_wf_extend<true, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
                 else if (ws->coop) k_wf_extend<false, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
                 else k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
-                if (timed) cudaEventRecord(ws->ev[3 * b + 1], st);
+                if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p) + 1], st);
                 k_wf_shade<<<shade_grid, 256, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur);
-                if (timed) cudaEventRecord(ws->ev[3 * b + 2], st);
+                if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p) + 2], st);
                 nl += 2;
             }
             it++;
@@ -616,13 +620,17 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         }
         if (e == cudaSuccess && timed) {
             float ms = 0.f;
-            if (first) { cudaEventElapsedTime(&ms, ws->ev[3 * batch], ws->ev[3 * batch + 1]); times->shade_ms += ms; times->shade_launches++; first = false; }
-            for (int b = 0; b < batch; b++) {
-                cudaEventElapsedTime(&ms, ws->ev[3 * b], ws->ev[3 * b + 1]); times->extend_ms += ms;
-                cudaEventElapsedTime(&ms, ws->ev[3 * b + 1], ws->ev[3 * b + 2]); times->shade_ms += ms;
+            if (first) { cudaEventElapsedTime(&ms, ws->ev[ev_begin], ws->ev[ev_begin + 1]); times->shade_ms += ms; times->shade_launches++; first = false; }
+            for (int p = 0; p < parts; p++) {
+                if (!timed_part[p]) continue;
+                for (int b = 0; b < batch; b++) {
+                    const int k = 3 * (b * parts + p);
+                    cudaEventElapsedTime(&ms, ws->ev[k], ws->ev[k + 1]); times->extend_ms += ms;
+                    cudaEventElapsedTime(&ms, ws->ev[k + 1], ws->ev[k + 2]); times->shade_ms += ms;
+                }
+                times->extend_launches += batch;
+                times->shade_launches += batch;
             }
-            times->extend_launches += batch;
-            times->shade_launches += batch;
         }
         if (active == 0) break;
     }

@@ -37,7 +37,7 @@ want = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "la
         "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio", "smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio"]
 traffic = {}
 with open(os.path.join(P, out + "_ncu_kernels.txt"), "w") as f:
-    f.write("# ncu --set full --clock-control none --import-source on, one launch each (steady state: launch #100 of a 64-spp frame, full 3.69 M-ray queue)\n")
+    f.write("# ncu --set full --clock-control none --import-source on, one launch each (steady state: launch #100 of a 64-spp frame, one part = half of the 3.69 M pixels per launch)\n")
     for name, kern in (("extend", "k_wf_extend"), ("shade", "k_wf_shade"), ("mega", "k_render_mega")):
         rep = os.path.join(G, "%s_%s.ncu-rep" % (tag, name))
         if not os.path.exists(rep): continue
