@@ -37,6 +37,8 @@ struct WfPart {
     uint32_t* qcount = nullptr;     // [0],[1] queue sizes, [2] fetch cursor of extend
     uint32_t* tile_count = nullptr; // per-tile survivor counts / offsets of the compaction
     uint32_t* h_qcount = nullptr;   // pinned
+    uint2* suspended[2] = {nullptr, nullptr};   // suspended traversals, [launch parity][extend thread][CRT_SUSPEND_WORDS]
+    uint32_t extend_launches = 0;   // parity of the next extend launch
     uint32_t cap = 0;               // pixels of this part
     uint32_t live = 0;              // queue length of the current batch (host copy)
     int cur = 0;
@@ -56,6 +58,8 @@ struct WavefrontState {
     size_t n = 0;
     int blocks_extend = 0, blocks_shade = 0;
     int fetch_lanes = CRT_FETCH_LANES, postpone_lanes = CRT_POSTPONE_LANES, coop = 0, shade_persistent = 1;   // tuning knobs (env CRT_FETCH_LANES / CRT_POSTPONE_LANES)
+    int drain_rounds = 4;            // env CRT_DRAIN_ROUNDS: rounds a warp keeps going after the queue ran out, then it suspends its rays (0 = never suspend)
+    long long drain_min_live = -1;   // env CRT_DRAIN_MIN_LIVE: suspend only while the part's queue is at least this long (-1 = one ray per extend thread)
     cudaEvent_t ev[3 * 16 * CRT_WF_MAX_PARTS + 2] = {};   // CRT_RENDER_TIME_KERNELS: begin pair + 3 events per (iteration, part) of a batch
 };
 
@@ -84,6 +88,20 @@ __device__ __forceinline__ void wf_store_rng(uint32_t* planes, size_t n, size_t 
 // warp, the first version, shuffles the queue a little at every departure; by iteration ~3000 of a 2000-spp
 // frame neighbouring entries came from unrelated pixels and shade ran 3x slower.)
 #define QUEUE_DEAD 0xffffffffu
+// A ray that extend parks (see k_wf_extend, "drain") is marked in its pixel's path state, twice:
+//  * C.x = PARKED_T instead of a hit distance: shade skips the pixel. Overwritten when the ray finishes.
+//  * the sign bit of A.w (throughput.x, never negative otherwise): the ray is served from the parked-ray list,
+//    so the queue fetch of extend skips the pixel. It has to outlive the ray (the list entry may be finished
+//    before another warp meets the pixel's queue entry), so it stays until shade rewrites A.
+// PARKED_LANE tags a lane's `pix` register while it runs a resumed ray.
+#define PARKED_T (-2.0f)
+#define PARKED_SIGN 0x80000000u
+#define PARKED_LANE 0x80000000u
+#define PIXEL_MASK 0x7fffffffu
+// One parked traversal: [0] = (pixel, stack depth), [1] = (t bits, winning primitive record), [2] = (winning id, -),
+// [3] = current node group, [4..] = the traversal stack. At most one per extend thread and launch; two lists per
+// part, written and read alternately (qcount[4 + parity] = length).
+#define CRT_SUSPEND_WORDS (4 + CRT_STACK_ENTRIES)
 #define CRT_COMPACT_TILE 2048   // entries per CTA (256 threads x 8)
 
 __global__ void __launch_bounds__(256) k_compact_count(const uint32_t* queue, const uint32_t* qcount, int cur, uint32_t* tile_count) {
@@ -194,7 +212,7 @@ __global__ void __launch_bounds__(256) k_wf_begin(RenderArgs a, WfView w, BeginQ
     }
     if (blockIdx.x == 0 && threadIdx.x < q.parts) {
         uint32_t* c = q.qcount[threadIdx.x];
-        c[0] = q.cap[threadIdx.x]; c[1] = 0u; c[2] = 0u;
+        c[0] = q.cap[threadIdx.x]; c[1] = 0u; c[2] = 0u; c[4] = 0u; c[5] = 0u;
     }
 }
 
@@ -223,12 +241,15 @@ struct WarpPool {
 #define CRT_EXTEND_MIN_BLOCKS (1024 / CRT_EXTEND_THREADS)
 #endif
 template <bool COUNT, bool COOP>
-__global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_wf_extend(SceneView scene, WfView w, const uint32_t* queue, uint32_t* qcount, int cur,
-                                                   unsigned long long* counters, int fetch_lanes, int postpone_lanes) {
-    (void)postpone_lanes;
+__global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_wf_extend(SceneView scene, WfView w, uint32_t* queue, uint32_t* qcount, int cur,
+                                                   unsigned long long* counters, int fetch_lanes, int drain_rounds,
+                                                   uint2* susp_out, const uint2* susp_in, int par) {
     __shared__ WarpPool pools[COOP ? CRT_EXTEND_THREADS / 32 : 1];
     WarpPool& S = pools[COOP ? threadIdx.x >> 5 : 0];
-    const uint32_t count = qcount[cur];
+    // work items: first the rays the previous launch parked (they are the long ones: started first, they have the
+    // whole launch to finish), then the queue
+    const uint32_t nres = qcount[4 + (par ^ 1)];
+    const uint32_t count = nres + qcount[cur];
     const int lane = threadIdx.x & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const float tmin = 0.001f;
@@ -241,7 +262,8 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
     uint32_t octinv = 0, ng_x = 0, ng_y = 0;
     int sp = 0;
     bool has_ray = false, exhausted = false;
-    uint32_t pix = 0;
+    uint32_t pix = 0;   // | PARKED_LANE while the lane runs a resumed ray
+    int drain = drain_rounds;
     while (true) {
         unsigned idle = __ballot_sync(0xffffffffu, !has_ray);
         if (!exhausted && __popc(idle) >= fetch_lanes) {
@@ -251,9 +273,20 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
             base = __shfl_sync(0xffffffffu, base, leader);
             if (base + (uint32_t)n >= count) exhausted = true;
             const uint32_t i = base + (uint32_t)__popc(idle & lt_mask);
-            if (!has_ray && i < count) pix = queue[i];
-            if (!has_ray && i < count && pix != QUEUE_DEAD) {
-                const float4 A = w.A[pix], B = w.B[pix];
+            const uint2* r = susp_in + (size_t)i * CRT_SUSPEND_WORDS;
+            bool take = !has_ray && i < count;
+            if (take) {
+                pix = i < nres ? (r[0].x | PARKED_LANE) : queue[i - nres];
+                take = pix != QUEUE_DEAD;
+            }
+            float4 A = make_float4(0.f, 0.f, 0.f, 0.f), B = A;
+            if (take) {
+                A = w.A[pix & PIXEL_MASK];
+                B = w.B[pix & PIXEL_MASK];
+                // a parked pixel met in the queue: its ray is in the list, not here
+                take = (pix & PARKED_LANE) || !(__float_as_uint(A.w) & PARKED_SIGN);
+            }
+            if (take) {
                 o = mk3(A.x, A.y, A.z);
                 d = mk3(B.x, B.y, B.z);
                 rec.t = INFINITY; rec.prim = 0u; rec.id = -1;
@@ -263,6 +296,13 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
                 const float ddz = fabsf(B.z) < tiny ? (B.z < 0.f ? -tiny : tiny) : B.z;
                 idx = 1.0f / ddx; idy = 1.0f / ddy; idz = 1.0f / ddz;
                 octinv = (ddx < 0.f ? 0u : 4u) | (ddy < 0.f ? 0u : 2u) | (ddz < 0.f ? 0u : 1u);
+                if (pix & PARKED_LANE) {
+                    // a traversal parked by the previous extend launch: closest hit so far, node group and stack come back
+                    const uint2 r0 = r[0], r1 = r[1], r2 = r[2], r3 = r[3];
+                    rec.t = __uint_as_float(r1.x); rec.prim = r1.y; rec.id = (int32_t)r2.x;
+                    sp = (int)r0.y; ng_x = r3.x; ng_y = r3.y;
+                    for (int k = 0; k < sp; k++) { const uint2 e = r[4 + k]; st.x[k] = e.x; st.y[k] = e.y; }
+                } else {
                 sp = 0; ng_x = 0u; ng_y = 0x80000000u;
                 if (COOP) {
                     S.ray[0][lane] = A.x; S.ray[1][lane] = A.y; S.ray[2][lane] = A.z;
@@ -279,14 +319,37 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
                     S.best[lane] = ((unsigned long long)__float_as_uint(rec.t) << 32) | (unsigned long long)(0xffffffffu - (uint32_t)rec.id);
                     S.win[lane] = rec.prim;
                 }
-                has_ray = true;
                 c_rays++;
+                }
+                has_ray = true;
             }
             idle = __ballot_sync(0xffffffffu, !has_ray);
         }
         if (idle == 0xffffffffu) {
             if (exhausted) break;
             continue;   // a refill that met only finished (dead) queue entries: fetch again
+        }
+        // drain: once the queue has run out a warp goes on for `drain_rounds` rounds, then parks what is left.
+        // The last rays of a launch are its longest (tens of node visits, each a dependent chain of loads)
+        // and would hold the kernel open, latency bound, with most SMs idle: measured 0.13 ms of a 0.27 ms
+        // launch. A parked ray's pixel is marked (PARKED_SIGN), shade skips it, and the next extend launch starts
+        // with the parked rays, each taken up where it stopped, alongside a full queue of other rays.
+        if (exhausted && drain_rounds > 0 && --drain < 0) {
+            if (has_ray) {
+                const uint32_t slot = atomicAdd(&qcount[4 + par], 1u);
+                uint2* r = susp_out + (size_t)slot * CRT_SUSPEND_WORDS;
+                r[0] = make_uint2(pix & PIXEL_MASK, (uint32_t)sp);
+                r[1] = make_uint2(__float_as_uint(rec.t), rec.prim);
+                r[2] = make_uint2((uint32_t)rec.id, 0u);
+                r[3] = make_uint2(ng_x, ng_y);
+                for (int k = 0; k < sp; k++) r[4 + k] = make_uint2(st.x[k], st.y[k]);
+                w.C[pix & PIXEL_MASK].x = PARKED_T;
+                if (!(pix & PARKED_LANE)) {
+                    uint32_t* aw = reinterpret_cast<uint32_t*>(&w.A[pix].w);
+                    *aw |= PARKED_SIGN;
+                }
+            }
+            break;
         }
 
         // node round: every lane with a ray visits its next wide node (a lane with a ray always has one pending)
@@ -372,6 +435,7 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
                 uint32_t win;
                 if (COOP) { win = S.win[lane]; t = __uint_as_float((uint32_t)(S.best[lane] >> 32)); }
                 else { win = rec.id >= 0 ? rec.prim : 0xffffffffu; t = rec.t; }
+                pix &= PIXEL_MASK;
                 float2* c = reinterpret_cast<float2*>(&w.C[pix]);
                 *c = make_float2(win != 0xffffffffu ? t : -1.f, __uint_as_float(win));
                 has_ray = false;
@@ -395,16 +459,18 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
 #ifndef CRT_SHADE_MIN_BLOCKS
 #define CRT_SHADE_MIN_BLOCKS 5
 #endif
-__global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderArgs a, WfView w, uint32_t* queue, uint32_t* qcount, int cur) {
+__global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderArgs a, WfView w, uint32_t* queue, uint32_t* qcount, int cur, int par) {
     const uint32_t count = qcount[cur];
     const uint32_t rounded = (count + 31u) & ~31u;
     const size_t n = (size_t)a.rc.width * a.rc.height;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
         bool keep = false;
         uint32_t pix = i < count ? queue[i] : QUEUE_DEAD;
+        // a parked pixel waits for extend to finish its ray: its entry stays, nothing else is touched
+        if (pix != QUEUE_DEAD && w.C[pix].x == PARKED_T) pix = QUEUE_DEAD;
         if (pix != QUEUE_DEAD) {
             const float4 A = w.A[pix], B = w.B[pix], C = w.C[pix];
-            vec3 o = mk3(A.x, A.y, A.z), d = mk3(B.x, B.y, B.z), thr = mk3(A.w, B.w, C.z);
+            vec3 o = mk3(A.x, A.y, A.z), d = mk3(B.x, B.y, B.z), thr = mk3(fabsf(A.w), B.w, C.z);   // |A.w|: PARKED_SIGN may be left on it
             const uint32_t book = __float_as_uint(C.w);
             int sample = (int)(book & 0xffffffu), bounce = (int)(book >> 24);
             Rng rng = wf_load_rng(a.fb.rng, n, pix);
@@ -477,7 +543,10 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
             }
         }
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) qcount[2] = 0u;   // fetch cursor of the next extend
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        qcount[2] = 0u;                // fetch cursor of the next extend
+        qcount[4 + (par ^ 1)] = 0u;    // the parked-ray list the extend before this shade has consumed: the next extend fills it
+    }
 }
 
 cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
@@ -496,7 +565,7 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
         const size_t cap = p == 0 ? s->n : ((tiles + (size_t)s->parts - 1) / (size_t)s->parts) * CRT_COMPACT_TILE;
         e = cudaMalloc(&q.queue[0], cap * sizeof(uint32_t));
         if (e == cudaSuccess) e = cudaMalloc(&q.queue[1], cap * sizeof(uint32_t));
-        if (e == cudaSuccess) e = cudaMalloc(&q.qcount, 4 * sizeof(uint32_t));
+        if (e == cudaSuccess) e = cudaMalloc(&q.qcount, 8 * sizeof(uint32_t));
         if (e == cudaSuccess) e = cudaMalloc(&q.tile_count, (tiles + 1) * sizeof(uint32_t));
         if (e == cudaSuccess) e = cudaMallocHost(&q.h_qcount, 4 * sizeof(uint32_t));
         if (e == cudaSuccess && p > 0) e = cudaEventCreateWithFlags(&q.ev_done, cudaEventDisableTiming);
@@ -510,6 +579,8 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
     if (const char* v = getenv("CRT_COOP")) s->coop = atoi(v);
     if (const char* v = getenv("CRT_SHADE_PERSISTENT")) s->shade_persistent = atoi(v);
     if (const char* v = getenv("CRT_POSTPONE_LANES")) s->postpone_lanes = atoi(v);
+    if (const char* v = getenv("CRT_DRAIN_ROUNDS")) s->drain_rounds = atoi(v);
+    if (const char* v = getenv("CRT_DRAIN_MIN_LIVE")) s->drain_min_live = atoll(v);
     if (s->fetch_lanes < 1) s->fetch_lanes = 1;
     if (s->fetch_lanes > 32) s->fetch_lanes = 32;
     if (const char* v = getenv("CRT_EXTEND_BLOCKS")) be = atoi(v);
@@ -525,6 +596,7 @@ void wavefront_destroy(WavefrontState* s) {
     cudaFree(s->A); cudaFree(s->B); cudaFree(s->C);
     for (WfPart& q : s->part) {
         cudaFree(q.queue[0]); cudaFree(q.queue[1]); cudaFree(q.qcount); cudaFree(q.tile_count);
+        cudaFree(q.suspended[0]); cudaFree(q.suspended[1]);
         if (q.h_qcount) cudaFreeHost(q.h_qcount);
         if (q.ev_done) cudaEventDestroy(q.ev_done);
     }
@@ -549,6 +621,10 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         for (int i = 0; i < ev_begin + 2 && e == cudaSuccess; i++) e = cudaEventCreate(&ws->ev[i]);
     if (e != cudaSuccess) return e;
     const size_t tiles_all = (ws->n + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE;
+    // rays are parked (see k_wf_extend) only by the plain kernel and only while the queue is longer than one
+    // launch's worth of threads: a short queue runs out at the first fetch and nothing would be gained
+    const bool suspend = ws->drain_rounds > 0 && !counted && !ws->coop;
+    const long long min_live = ws->drain_min_live >= 0 ? ws->drain_min_live : (long long)grid_e * CRT_EXTEND_THREADS;
     BeginQueues bq = {};
     bq.parts = parts;
     for (int p = 0; p < parts; p++) {
@@ -557,11 +633,14 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         size_t cap = my_tiles * CRT_COMPACT_TILE;
         if (my_tiles > 0 && (tiles_all - 1) % (size_t)parts == (size_t)p) cap -= tiles_all * CRT_COMPACT_TILE - ws->n;   // the partial last tile
         q.cap = (uint32_t)cap; q.live = q.cap; q.cur = 0; q.done = q.cap == 0u;
+        for (int k = 0; k < 2 && e == cudaSuccess && suspend && !q.suspended[k]; k++)
+            e = cudaMalloc(&q.suspended[k], (size_t)grid_e * CRT_EXTEND_THREADS * CRT_SUSPEND_WORDS * sizeof(uint2));
         // per-kernel times only mean something when the kernels run one after the other: a timed render keeps
         // the same launches (one per part) but puts them all on the caller's stream
         q.stream = (p == 0 || timed) ? stream : ws->side_stream[p];
         bq.queue[p] = q.queue[0]; bq.qcount[p] = q.qcount; bq.cap[p] = q.cap;
     }
+    if (e != cudaSuccess) return e;
     uint32_t nl = 0;
     if (timed) cudaEventRecord(ws->ev[ev_begin], stream);
     k_wf_begin<<<grid_s, 256, 0, stream>>>(a, w, bq);
@@ -572,7 +651,9 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         e = cudaEventRecord(ws->ev_fork, stream);
         for (int p = 1; p < parts && e == cudaSuccess; p++) e = cudaStreamWaitEvent(ws->side_stream[p], ws->ev_fork, 0);
     }
-    const long long max_iters = (long long)a.rc.spp * a.rc.max_bounces + 1;
+    // one iteration per path segment, plus the iterations in which a pixel's ray was parked (every parked ray
+    // advances at least drain_rounds node visits per launch); a bound against a hang, not a tuning knob
+    const long long max_iters = ((long long)a.rc.spp * a.rc.max_bounces + 1) * 256;
     long long it = 0;
     bool first = true;
     while (e == cudaSuccess && it < max_iters) {
@@ -586,12 +667,14 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                 cudaStream_t st = q.stream;
                 // shade: grid-stride over 148 x occupancy CTAs (CRT_SHADE_PERSISTENT=0: one CTA per 256 queue entries)
                 const int shade_grid = ws->shade_persistent ? grid_s : (int)((q.live + 255u) / 256u);
+                const int drain = (suspend && (long long)q.live >= min_live) ? ws->drain_rounds : 0;
+                const int par = (int)(q.extend_launches++ & 1u);
                 if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p)], st);
-                if (counted) k_wf_extend<true, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
-                else if (ws->coop) k_wf_extend<false, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
-                else k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, ws->postpone_lanes);
+                if (counted) k_wf_extend<true, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par);
+                else if (ws->coop) k_wf_extend<false, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par);
+                else k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par);
                 if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p) + 1], st);
-                k_wf_shade<<<shade_grid, 256, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur);
+                k_wf_shade<<<shade_grid, 256, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur, par);
                 if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p) + 2], st);
                 nl += 2;
             }

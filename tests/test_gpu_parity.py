@@ -91,6 +91,52 @@ def test_wavefront_equals_megakernel_bitwise(crt):
     sc.free()
 
 
+@pytest.mark.parametrize("rounds,parts", [(1, 2), (3, 1), (2, 3)])
+def test_parked_rays_resume_bitwise(crt, rounds, parts, monkeypatch):
+    """extend parks the rays that are still in flight when its queue runs out (k_wf_extend "drain") and the next
+    launch resumes them from the saved stack. Forced here on every launch of a small frame (a ray then needs
+    many launches); the frame must equal the megakernel's bit for bit, ray count included."""
+    sc = crt.builtin_scene("cornell_blob", 48)
+    W, H = 200, 120
+    r = make_renderer(crt, sc, W, H, crt.MODE_MEGAKERNEL)
+    st = r.render(5, 20)
+    want = (r.accum().copy(), r.image_rgba8().copy(), r.rng_state().copy(), int(st.rays))
+    r.close()
+    monkeypatch.setenv("CRT_DRAIN_ROUNDS", str(rounds))
+    monkeypatch.setenv("CRT_DRAIN_MIN_LIVE", "0")
+    monkeypatch.setenv("CRT_WF_PARTS", str(parts))
+    r = make_renderer(crt, sc, W, H, crt.MODE_WAVEFRONT)
+    for _ in range(2):                                   # second frame: the pools are reused
+        r.initialize(SEED, 0)
+        st = r.render(5, 20)
+        assert np.array_equal(want[0].view(np.uint32), r.accum().view(np.uint32))
+        assert np.array_equal(want[1], r.image_rgba8())
+        assert np.array_equal(want[2], r.rng_state())
+        assert want[3] == int(st.rays)
+    r.close()
+    sc.free()
+
+
+def test_parked_rays_full_size_default_settings(crt, monkeypatch):
+    """Default settings park rays only on long queues: a 2560x1440 frame, against a run with parking off."""
+    sc = crt.builtin_scene("cornell_blob")
+    W, H = 2560, 1440
+    out = []
+    for rounds in ("0", None):
+        if rounds is None:
+            monkeypatch.delenv("CRT_DRAIN_ROUNDS", raising=False)
+        else:
+            monkeypatch.setenv("CRT_DRAIN_ROUNDS", rounds)
+        r = make_renderer(crt, sc, W, H, crt.MODE_WAVEFRONT)
+        st = r.render(3, 20)
+        out.append((r.accum().copy(), r.rng_state().copy(), int(st.rays)))
+        r.close()
+    assert np.array_equal(out[0][0].view(np.uint32), out[1][0].view(np.uint32))
+    assert np.array_equal(out[0][1], out[1][1])
+    assert out[0][2] == out[1][2]
+    sc.free()
+
+
 def test_rng_state_matches_curand_init(crt):
     sc = crt.builtin_scene("cornell")
     r = crt.Renderer(64, 48, mode=crt.MODE_MEGAKERNEL)
