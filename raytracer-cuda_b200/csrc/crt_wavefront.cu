@@ -660,7 +660,11 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         int active = 0;
         bool timed_part[CRT_WF_MAX_PARTS];
         for (int p = 0; p < CRT_WF_MAX_PARTS; p++) timed_part[p] = p < parts && !ws->part[p].done;
-        for (int b = 0; b < batch; b++) {
+        // iterations until the host looks at the queue lengths again: 16, but no more than can still be needed
+        // when no ray gets parked (one iteration per path segment), and short batches for the stragglers after that
+        const long long needed = (long long)a.rc.spp * a.rc.max_bounces + 1 - it;
+        const int nb = needed >= batch ? batch : (needed > 0 ? (int)needed : 4);
+        for (int b = 0; b < nb; b++) {
             for (int p = 0; p < parts; p++) {
                 WfPart& q = ws->part[p];
                 if (q.done) continue;
@@ -706,13 +710,13 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
             if (first) { cudaEventElapsedTime(&ms, ws->ev[ev_begin], ws->ev[ev_begin + 1]); times->shade_ms += ms; times->shade_launches++; first = false; }
             for (int p = 0; p < parts; p++) {
                 if (!timed_part[p]) continue;
-                for (int b = 0; b < batch; b++) {
+                for (int b = 0; b < nb; b++) {
                     const int k = 3 * (b * parts + p);
                     cudaEventElapsedTime(&ms, ws->ev[k], ws->ev[k + 1]); times->extend_ms += ms;
                     cudaEventElapsedTime(&ms, ws->ev[k + 1], ws->ev[k + 2]); times->shade_ms += ms;
                 }
-                times->extend_launches += batch;
-                times->shade_launches += batch;
+                times->extend_launches += nb;
+                times->shade_launches += nb;
             }
         }
         if (active == 0) break;
