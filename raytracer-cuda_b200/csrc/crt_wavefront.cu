@@ -463,13 +463,25 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
     const uint32_t count = qcount[cur];
     const uint32_t rounded = (count + 31u) & ~31u;
     const size_t n = (size_t)a.rc.width * a.rc.height;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
+    const uint32_t first = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    uint32_t pix_next = first < count ? queue[first] : QUEUE_DEAD;
+    for (uint32_t i = first; i < rounded; i += stride) {
         bool keep = false;
-        uint32_t pix = i < count ? queue[i] : QUEUE_DEAD;
-        // a parked pixel waits for extend to finish its ray: its entry stays, nothing else is touched
-        if (pix != QUEUE_DEAD && w.C[pix].x == PARKED_T) pix = QUEUE_DEAD;
+        const uint32_t pix = pix_next;
+        // the thread's next entry: its queue word is loaded now and its path state prefetched below, so that the
+        // next trip does not start with a chain of DRAM latencies (queue -> state -> primitive record)
+        pix_next = (i + stride < count) ? queue[i + stride] : QUEUE_DEAD;
         if (pix != QUEUE_DEAD) {
             const float4 A = w.A[pix], B = w.B[pix], C = w.C[pix];
+            if (C.x == PARKED_T) continue;   // a parked pixel waits for extend to finish its ray: nothing is touched
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(a.fb.accum + pix));   // read only when a path ends, late in the body
+            if (pix_next != QUEUE_DEAD) {
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(w.A + pix_next));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(w.B + pix_next));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(w.C + pix_next));
+#pragma unroll
+                for (int k = 0; k < 6; k++) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.fb.rng + (size_t)k * n + pix_next));
+            }
             vec3 o = mk3(A.x, A.y, A.z), d = mk3(B.x, B.y, B.z), thr = mk3(fabsf(A.w), B.w, C.z);   // |A.w|: PARKED_SIGN may be left on it
             const uint32_t book = __float_as_uint(C.w);
             int sample = (int)(book & 0xffffffu), bounce = (int)(book >> 24);
