@@ -169,7 +169,7 @@ typedef struct crt_stats {
     uint32_t extend_launches;
     uint32_t shade_launches;
     uint32_t bvh_giants;       /* primitives kept out of the BVH and tested by every ray (<= 4)  */
-    uint32_t reserved32;
+    float    tail_ms;          /* wavefront, with CRT_RENDER_TIME_KERNELS: the closing extend + k_wf_tail launches   */
     uint64_t reserved[1];
 } crt_stats;
 

@@ -262,7 +262,7 @@ static int render_impl(crt_ctx* ctx, const crt_render_params* p, bool counted) {
     ctx->stats.prims_tested = c[3];
     ctx->stats.kernel_launches = launches;
     if (mega) { kt.extend_ms = ctx->stats.render_ms; kt.extend_launches = 1; }
-    ctx->stats.extend_ms = kt.extend_ms; ctx->stats.shade_ms = kt.shade_ms;
+    ctx->stats.extend_ms = kt.extend_ms; ctx->stats.shade_ms = kt.shade_ms; ctx->stats.tail_ms = kt.tail_ms;
     ctx->stats.extend_launches = kt.extend_launches; ctx->stats.shade_launches = kt.shade_launches;
     return CRT_OK;
 }

@@ -26,7 +26,7 @@ struct RenderArgs {
 };
 
 struct KernelTimes {
-    float extend_ms = 0.f, shade_ms = 0.f;
+    float extend_ms = 0.f, shade_ms = 0.f, tail_ms = 0.f;
     uint32_t extend_launches = 0, shade_launches = 0;
 };
 

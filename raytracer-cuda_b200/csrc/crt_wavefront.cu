@@ -16,6 +16,8 @@
 //   A = (o.x, o.y, o.z, thr.x)   B = (d.x, d.y, d.z, thr.y)   C = (t, prim, thr.z, book)
 //   book = sample index (bits 0-23) | bounce (bits 24-31)
 #include <cuda_runtime.h>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 
 #include "crt_internal.h"
@@ -43,6 +45,7 @@ struct WfPart {
     uint32_t live = 0;              // queue length of the current batch (host copy)
     int cur = 0;
     bool done = false;
+    int tail = 0;                   // 0 = wavefront iterations, 1 = handed to k_wf_tail (closing extend still to run), 2 = tail stages
     cudaStream_t stream = nullptr;  // part 0 runs on the caller's stream
     cudaEvent_t ev_done = nullptr;
 };
@@ -59,8 +62,13 @@ struct WavefrontState {
     int blocks_extend = 0, blocks_shade = 0;
     int fetch_lanes = CRT_FETCH_LANES, postpone_lanes = CRT_POSTPONE_LANES, coop = 0, shade_persistent = 1;   // tuning knobs (env CRT_FETCH_LANES / CRT_POSTPONE_LANES)
     int drain_rounds = 4;            // env CRT_DRAIN_ROUNDS: rounds a warp keeps going after the queue ran out, then it suspends its rays (0 = never suspend)
+    long long tail_live = 150000;    // env CRT_TAIL_LIVE: a part whose queue is at most this long is finished by k_wf_tail stages (0 = never)
+    int tail_iters = 64;             // env CRT_TAIL_ITERS: path segments per pixel and tail stage
+    int tail_lanes_min = 1;          // env CRT_TAIL_LANES_MIN: lanes of a warp that take a pixel, at least
+    int tail_blocks = 4;             // resident k_wf_tail CTAs per SM (occupancy query)
+    int tail_shade_lanes = 8;        // env CRT_TAIL_SHADE_LANES: of 32; lanes that have to be waiting before a tail warp runs its shade step
     long long drain_min_live = -1;   // env CRT_DRAIN_MIN_LIVE: suspend only while the part's queue is at least this long (-1 = one ray per extend thread)
-    cudaEvent_t ev[3 * 16 * CRT_WF_MAX_PARTS + 2] = {};   // CRT_RENDER_TIME_KERNELS: begin pair + 3 events per (iteration, part) of a batch
+    cudaEvent_t ev[3 * 16 * CRT_WF_MAX_PARTS + 2 + 2 * CRT_WF_MAX_PARTS] = {};   // CRT_RENDER_TIME_KERNELS: begin pair + 3 events per (iteration, part) of a batch
 };
 
 struct WfView {
@@ -455,6 +463,63 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
     }
 }
 
+// One shade step of a pixel's path, on registers: consume the hit (t < 0 = miss), continue / finish the path,
+// start the pixel's next sample when the path ended, draw Russian roulette for the next bounce. Returns false
+// when the pixel's last sample is done. Shared by k_wf_shade (one step per launch) and k_wf_tail (looped).
+__device__ __forceinline__ bool shade_step(const RenderArgs& a, uint32_t pix, vec3& o, vec3& d, vec3& thr, int& sample, int& bounce, Rng& rng,
+                                           float hit_t, uint32_t hit_prim, float4& acc, bool& touched) {
+    bool keep;
+    bool ended = false;
+    vec3 result = mk3(0.f, 0.f, 0.f);
+    if (!(hit_t < 0.f)) {                                  // extend stores t = -1 for a miss
+        HitRec h;
+        h.t = hit_t; h.prim = hit_prim; h.id = 0;
+        const Surface s = surface_at(a.scene, h, o, d);
+        if (s.mat < a.scene.num_mats) {
+            const MatRec m = a.scene.mats[s.mat];
+            vec3 att, no, nd;
+            if (scatter(m, s, d, rng, att, no, nd)) {
+                thr = v_mul(thr, att);
+                o = no;
+                d = nd;
+            } else {
+                result = emitted(m);
+                ended = true;
+            }
+        }
+    } else {
+        result = v_mul(thr, background(d));
+        ended = true;
+    }
+    if (!ended) bounce++;
+    // Finish / regenerate / Russian roulette, in the megakernel's order: a path that ends
+    // adds its radiance and the pixel's next sample starts at once; RR is drawn before the
+    // next closest-hit query whenever bounce >= min_bounces (CUDAKernels.h:113-121).
+    keep = true;
+    while (true) {
+        if (ended) {
+            if (!touched) { acc = a.fb.accum[pix]; touched = true; }
+            acc.x = f_add(acc.x, result.x); acc.y = f_add(acc.y, result.y); acc.z = f_add(acc.z, result.z);
+            sample++;
+            if (sample >= a.rc.spp) { keep = false; break; }
+            const int x = (int)(pix % (uint32_t)a.rc.width), y = (int)(pix / (uint32_t)a.rc.width);
+            camera_ray(a.cam, x, y, a.rc.width, a.rc.height, rng, o, d);
+            thr = mk3(1.f, 1.f, 1.f);
+            bounce = 0;
+            result = mk3(0.f, 0.f, 0.f);
+            ended = false;
+        }
+        if (bounce >= a.rc.max_bounces) { ended = true; continue; }   // exhausted: black
+        if (bounce >= a.rc.min_bounces) {
+            const float p = fminf(fmaxf(thr.x, fmaxf(thr.y, thr.z)), a.rc.rr_max_prob);
+            if (rng_uniform(rng) > p) { ended = true; continue; }
+            thr = v_scale(thr, f_rcp(p));
+        }
+        break;
+    }
+    return keep;
+}
+
 // ---- shade: consume the hit, continue / finish / regenerate, Russian roulette, compact -----------------
 #ifndef CRT_SHADE_MIN_BLOCKS
 #define CRT_SHADE_MIN_BLOCKS 5
@@ -486,56 +551,9 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
             const uint32_t book = __float_as_uint(C.w);
             int sample = (int)(book & 0xffffffu), bounce = (int)(book >> 24);
             Rng rng = wf_load_rng(a.fb.rng, n, pix);
-            bool ended = false;
-            vec3 result = mk3(0.f, 0.f, 0.f);
-            if (!(C.x < 0.f)) {                                  // extend stores t = -1 for a miss
-                HitRec h;
-                h.t = C.x; h.prim = __float_as_uint(C.y); h.id = 0;
-                const Surface s = surface_at(a.scene, h, o, d);
-                if (s.mat < a.scene.num_mats) {
-                    const MatRec m = a.scene.mats[s.mat];
-                    vec3 att, no, nd;
-                    if (scatter(m, s, d, rng, att, no, nd)) {
-                        thr = v_mul(thr, att);
-                        o = no;
-                        d = nd;
-                    } else {
-                        result = emitted(m);
-                        ended = true;
-                    }
-                }
-            } else {
-                result = v_mul(thr, background(d));
-                ended = true;
-            }
-            if (!ended) bounce++;
-            // Finish / regenerate / Russian roulette, in the megakernel's order: a path that ends
-            // adds its radiance and the pixel's next sample starts at once; RR is drawn before the
-            // next closest-hit query whenever bounce >= min_bounces (CUDAKernels.h:113-121).
-            keep = true;
             bool touched = false;
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-            while (true) {
-                if (ended) {
-                    if (!touched) { acc = a.fb.accum[pix]; touched = true; }
-                    acc.x = f_add(acc.x, result.x); acc.y = f_add(acc.y, result.y); acc.z = f_add(acc.z, result.z);
-                    sample++;
-                    if (sample >= a.rc.spp) { keep = false; break; }
-                    const int x = (int)(pix % (uint32_t)a.rc.width), y = (int)(pix / (uint32_t)a.rc.width);
-                    camera_ray(a.cam, x, y, a.rc.width, a.rc.height, rng, o, d);
-                    thr = mk3(1.f, 1.f, 1.f);
-                    bounce = 0;
-                    result = mk3(0.f, 0.f, 0.f);
-                    ended = false;
-                }
-                if (bounce >= a.rc.max_bounces) { ended = true; continue; }   // exhausted: black
-                if (bounce >= a.rc.min_bounces) {
-                    const float p = fminf(fmaxf(thr.x, fmaxf(thr.y, thr.z)), a.rc.rr_max_prob);
-                    if (rng_uniform(rng) > p) { ended = true; continue; }
-                    thr = v_scale(thr, f_rcp(p));
-                }
-                break;
-            }
+            keep = shade_step(a, pix, o, d, thr, sample, bounce, rng, C.x, __float_as_uint(C.y), acc, touched);
             if (touched) {
                 if (!keep) {
                     acc.w += (float)a.rc.spp;
@@ -559,6 +577,99 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
         qcount[2] = 0u;                // fetch cursor of the next extend
         qcount[4 + (par ^ 1)] = 0u;    // the parked-ray list the extend before this shade has consumed: the next extend fills it
     }
+}
+
+// ---- tail: the last pixels of a frame, a thread per pixel for many iterations at a time ------------------
+// A pixel's samples are sequential (its cuRAND stream), so the frame ends with a few pixels (those with the
+// longest paths) that still owe hundreds of iterations. With a short queue an iteration costs what its longest
+// ray costs (~0.1 ms, latency bound) while tracing almost nothing: measured on the Cornell+blob frame, the
+// iterations with fewer than 150 k live pixels per part were 4 % of the rays and 10 % of the frame time.
+// Once a part's queue is that short the host stops iterating it: after one closing extend (nothing parked), this
+// kernel takes every remaining pixel with one thread that alternates shade_step and a whole closest-hit query
+// (the megakernel's loop, entered in the middle of a path) for up to `max_iters` path segments; pixels that are
+// not finished by then are written back in the "after extend" form, the queue is compacted and the next stage
+// runs on what is left. Only the first `lanes` lanes of a warp take a pixel: the fewer pixels are left, the more
+// warps they are spread over, because the latency of an iteration in a warp whose lanes are all at different
+// points of different paths grows with the number of lanes (their branches are issued one after the other).
+// Same operations in the same order per pixel as the wavefront iterations, so the frame's bits do not change.
+#ifndef CRT_TAIL_THREADS
+#define CRT_TAIL_THREADS 128
+#endif
+__global__ void __launch_bounds__(CRT_TAIL_THREADS) k_wf_tail(RenderArgs a, WfView w, uint32_t* queue, const uint32_t* qcount, int cur, int lanes, int max_iters, int shade_lanes) {
+    const uint32_t count = qcount[cur];
+    const size_t n = (size_t)a.rc.width * a.rc.height;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, warps = (gridDim.x * blockDim.x) >> 5;
+    uint32_t rays = 0;
+    for (uint32_t base = warp * (uint32_t)lanes; base < count; base += warps * (uint32_t)lanes) {
+        const uint32_t i = base + lane;
+        uint32_t pix = QUEUE_DEAD;
+        if (lane < (uint32_t)lanes && i < count) pix = queue[i];
+        bool alive = pix != QUEUE_DEAD;
+        vec3 thr = mk3(0.f, 0.f, 0.f);
+        int sample = 0, bounce = 0, it = 0;
+        Rng rng = {};
+        float hit_t = -1.f;
+        uint32_t hit_prim = 0u;
+        bool touched = false, need_shade = true;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        Traverser tr;
+        TravStack st;
+        tr.o = mk3(0.f, 0.f, 0.f); tr.d = mk3(0.f, 0.f, 1.f);
+        if (alive) {
+            const float4 A = w.A[pix], B = w.B[pix], C = w.C[pix];
+            tr.o = mk3(A.x, A.y, A.z); tr.d = mk3(B.x, B.y, B.z); thr = mk3(fabsf(A.w), B.w, C.z);
+            const uint32_t book = __float_as_uint(C.w);
+            sample = (int)(book & 0xffffffu); bounce = (int)(book >> 24);
+            rng = wf_load_rng(a.fb.rng, n, pix);
+            hit_t = C.x;
+            hit_prim = __float_as_uint(C.y);
+        }
+        // The lanes of the warp advance their traversals together, one wide-node visit per trip (Traverser::step);
+        // a lane whose query has finished runs its shade step at the top of the next trip and joins the others
+        // again with its next ray, instead of all lanes waiting for the warp's longest ray before any of them shades.
+        // The shade step waits until `shade_lanes` lanes need it (or no lane has a node left to visit), so that its
+        // long, branchy body is issued for several lanes at a time (the dynamic-fetch trade of k_wf_extend).
+        while (true) {
+            const unsigned want_shade = __ballot_sync(0xffffffffu, alive && need_shade);
+            const unsigned stepping = __ballot_sync(0xffffffffu, alive && !need_shade);
+            if ((want_shade | stepping) == 0u) break;
+            if (alive && need_shade && (__popc(want_shade) >= shade_lanes || stepping == 0u)) {
+                vec3 o = tr.o, d = tr.d;
+                if (shade_step(a, pix, o, d, thr, sample, bounce, rng, hit_t, hit_prim, acc, touched)) {
+                    tr.begin(o, d, 0.001f, INFINITY);
+                    trace_giants<false>(a.scene, o, d, 0.001f, tr.rec, nullptr);
+                    rays++;
+                    need_shade = false;
+                } else {
+                    acc.w += (float)a.rc.spp;
+                    if (!(a.flags & CRT_RENDER_NO_TONEMAP))
+                        a.fb.rgba8[pix] = pack_rgba8(v_scale(mk3(acc.x, acc.y, acc.z), f_div(1.f, acc.w)));
+                    a.fb.accum[pix] = acc;
+                    wf_store_rng(a.fb.rng, n, pix, rng);
+                    queue[i] = QUEUE_DEAD;
+                    alive = false;
+                }
+            }
+            __syncwarp();
+            if (alive && !need_shade && tr.step<false>(a.scene, st, nullptr)) {
+                const bool hit = tr.rec.id >= 0;
+                hit_t = hit ? tr.rec.t : -1.f;
+                hit_prim = tr.rec.prim;
+                need_shade = true;
+                if (++it >= max_iters) {   // the state k_wf_extend leaves behind: ray, throughput, book-keeping and the hit just found
+                    w.A[pix] = make_float4(tr.o.x, tr.o.y, tr.o.z, thr.x);
+                    w.B[pix] = make_float4(tr.d.x, tr.d.y, tr.d.z, thr.y);
+                    w.C[pix] = make_float4(hit_t, __uint_as_float(hit_prim), thr.z, __uint_as_float((uint32_t)sample | ((uint32_t)bounce << 24)));
+                    if (touched) a.fb.accum[pix] = acc;
+                    wf_store_rng(a.fb.rng, n, pix, rng);
+                    alive = false;
+                }
+            }
+        }
+    }
+    rays = __reduce_add_sync(0xffffffffu, rays);
+    if ((threadIdx.x & 31) == 0 && rays) atomicAdd(&a.fb.counters[0], (unsigned long long)rays);
 }
 
 cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
@@ -593,6 +704,11 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
     if (const char* v = getenv("CRT_POSTPONE_LANES")) s->postpone_lanes = atoi(v);
     if (const char* v = getenv("CRT_DRAIN_ROUNDS")) s->drain_rounds = atoi(v);
     if (const char* v = getenv("CRT_DRAIN_MIN_LIVE")) s->drain_min_live = atoll(v);
+    if (const char* v = getenv("CRT_TAIL_LIVE")) s->tail_live = atoll(v);
+    if (const char* v = getenv("CRT_TAIL_SHADE_LANES")) s->tail_shade_lanes = atoi(v);
+    if (const char* v = getenv("CRT_TAIL_ITERS")) s->tail_iters = atoi(v) > 0 ? atoi(v) : 1;
+    if (const char* v = getenv("CRT_TAIL_LANES_MIN")) s->tail_lanes_min = atoi(v) < 1 ? 1 : (atoi(v) > 32 ? 32 : atoi(v));
+    { int bt = 0; if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bt, k_wf_tail, CRT_TAIL_THREADS, 0) == cudaSuccess && bt > 0) s->tail_blocks = bt; }
     if (s->fetch_lanes < 1) s->fetch_lanes = 1;
     if (s->fetch_lanes > 32) s->fetch_lanes = 32;
     if (const char* v = getenv("CRT_EXTEND_BLOCKS")) be = atoi(v);
@@ -630,7 +746,7 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
     const int parts = ws->parts;
     const int ev_begin = 3 * batch * CRT_WF_MAX_PARTS;
     if (timed && !ws->ev[0])
-        for (int i = 0; i < ev_begin + 2 && e == cudaSuccess; i++) e = cudaEventCreate(&ws->ev[i]);
+        for (int i = 0; i < ev_begin + 2 + 2 * CRT_WF_MAX_PARTS && e == cudaSuccess; i++) e = cudaEventCreate(&ws->ev[i]);
     if (e != cudaSuccess) return e;
     const size_t tiles_all = (ws->n + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE;
     // rays are parked (see k_wf_extend) only by the plain kernel and only while the queue is longer than one
@@ -644,7 +760,7 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         const size_t my_tiles = (tiles_all + (size_t)parts - 1 - (size_t)p) / (size_t)parts;
         size_t cap = my_tiles * CRT_COMPACT_TILE;
         if (my_tiles > 0 && (tiles_all - 1) % (size_t)parts == (size_t)p) cap -= tiles_all * CRT_COMPACT_TILE - ws->n;   // the partial last tile
-        q.cap = (uint32_t)cap; q.live = q.cap; q.cur = 0; q.done = q.cap == 0u;
+        q.cap = (uint32_t)cap; q.live = q.cap; q.cur = 0; q.done = q.cap == 0u; q.tail = 0;
         for (int k = 0; k < 2 && e == cudaSuccess && suspend && !q.suspended[k]; k++)
             e = cudaMalloc(&q.suspended[k], (size_t)grid_e * CRT_EXTEND_THREADS * CRT_SUSPEND_WORDS * sizeof(uint2));
         // per-kernel times only mean something when the kernels run one after the other: a timed render keeps
@@ -668,10 +784,13 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
     const long long max_iters = ((long long)a.rc.spp * a.rc.max_bounces + 1) * 256;
     long long it = 0;
     bool first = true;
+    // CRT_WF_TRACE=1: one stderr line per batch (iteration, queue lengths, host wall clock) for tuning runs
+    const bool trace = getenv("CRT_WF_TRACE") != nullptr;
+    const auto trace_t0 = std::chrono::steady_clock::now();
     while (e == cudaSuccess && it < max_iters) {
         int active = 0;
-        bool timed_part[CRT_WF_MAX_PARTS];
-        for (int p = 0; p < CRT_WF_MAX_PARTS; p++) timed_part[p] = p < parts && !ws->part[p].done;
+        bool timed_part[CRT_WF_MAX_PARTS], tail_part[CRT_WF_MAX_PARTS];
+        for (int p = 0; p < CRT_WF_MAX_PARTS; p++) { timed_part[p] = p < parts && !ws->part[p].done; tail_part[p] = p < parts && ws->part[p].tail != 0; }
         // iterations until the host looks at the queue lengths again: 16, but no more than can still be needed
         // when no ray gets parked (one iteration per path segment), and short batches for the stragglers after that
         const long long needed = (long long)a.rc.spp * a.rc.max_bounces + 1 - it;
@@ -681,6 +800,30 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                 WfPart& q = ws->part[p];
                 if (q.done) continue;
                 cudaStream_t st = q.stream;
+                if (q.tail) {   // one tail stage per batch (the first one after a closing extend that also completes the parked rays)
+                    if (b > 0) continue;
+                    if (timed) cudaEventRecord(ws->ev[ev_begin + 2 + 2 * p], st);
+                    if (q.tail == 1) {
+                        const int par = (int)(q.extend_launches++ & 1u);
+                        k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, 0, q.suspended[par], q.suspended[par ^ 1], par);
+                        q.tail = 2;
+                        nl++;
+                    }
+                    // spread the pixels over the warps the machine holds (shared by the parts that are in their tail)
+                    int tail_parts = 0;
+                    for (int k = 0; k < parts; k++) tail_parts += (!ws->part[k].done && ws->part[k].tail) ? 1 : 0;
+                    const long long warps_resident = (long long)num_sms * ws->tail_blocks * (CRT_TAIL_THREADS / 32) / (tail_parts > 0 ? tail_parts : 1);
+                    long long lanes = ((long long)q.live + warps_resident - 1) / (warps_resident > 0 ? warps_resident : 1);
+                    if (lanes < ws->tail_lanes_min) lanes = ws->tail_lanes_min;
+                    if (lanes > 32) lanes = 32;
+                    const long long tail_warps = ((long long)q.live + lanes - 1) / lanes;
+                    const int tail_grid = (int)((tail_warps * 32 + CRT_TAIL_THREADS - 1) / CRT_TAIL_THREADS);
+                    const int shade_lanes = (int)(lanes * ws->tail_shade_lanes / 32) > 1 ? (int)(lanes * ws->tail_shade_lanes / 32) : 1;
+                    k_wf_tail<<<tail_grid, CRT_TAIL_THREADS, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur, (int)lanes, ws->tail_iters, shade_lanes);
+                    if (timed) cudaEventRecord(ws->ev[ev_begin + 3 + 2 * p], st);
+                    nl++;
+                    continue;
+                }
                 // shade: grid-stride over 148 x occupancy CTAs (CRT_SHADE_PERSISTENT=0: one CTA per 256 queue entries)
                 const int shade_grid = ws->shade_persistent ? grid_s : (int)((q.live + 255u) / 256u);
                 const int drain = (suspend && (long long)q.live >= min_live) ? ws->drain_rounds : 0;
@@ -722,6 +865,10 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
             if (first) { cudaEventElapsedTime(&ms, ws->ev[ev_begin], ws->ev[ev_begin + 1]); times->shade_ms += ms; times->shade_launches++; first = false; }
             for (int p = 0; p < parts; p++) {
                 if (!timed_part[p]) continue;
+                if (tail_part[p]) {
+                    cudaEventElapsedTime(&ms, ws->ev[ev_begin + 2 + 2 * p], ws->ev[ev_begin + 3 + 2 * p]); times->tail_ms += ms;
+                    continue;
+                }
                 for (int b = 0; b < nb; b++) {
                     const int k = 3 * (b * parts + p);
                     cudaEventElapsedTime(&ms, ws->ev[k], ws->ev[k + 1]); times->extend_ms += ms;
@@ -731,6 +878,15 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                 times->shade_launches += nb;
             }
         }
+        // a part whose queue has become short leaves the wavefront iterations for the tail stages
+        for (int p = 0; p < parts && !counted && !ws->coop; p++) {
+            WfPart& q = ws->part[p];
+            if (!q.done && !q.tail && (long long)q.live <= ws->tail_live) q.tail = 1;
+        }
+        if (trace)
+            fprintf(stderr, "wf_trace it=%lld live=%u,%u,%u,%u ms=%.3f extend_ms=%.3f shade_ms=%.3f\n", it, ws->part[0].live, ws->part[1].live,
+                    ws->part[2].live, ws->part[3].live, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - trace_t0).count(),
+                    timed ? times->extend_ms : 0.0, timed ? times->shade_ms : 0.0);
         if (active == 0) break;
     }
     // every part's stream was synchronised by the host above, so work queued on `stream` after this call is ordered

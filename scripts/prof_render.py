@@ -14,6 +14,7 @@ ap.add_argument("--spp", type=int, default=4)
 ap.add_argument("--bounces", type=int, default=20)
 ap.add_argument("--reps", type=int, default=1)
 ap.add_argument("--counted", action="store_true")
+ap.add_argument("--time-kernels", action="store_true")
 a = ap.parse_args()
 crt = importlib.import_module("raytracer-cuda_b200")
 sc = crt.builtin_scene(a.scene, a.param)
@@ -22,7 +23,7 @@ r.set_scene(sc)
 r.update_camera(sc.camera)
 r.initialize(crt.REFERENCE_SEED, 0)
 for i in range(a.reps):
-    st = r.render(a.spp, a.bounces, counted=a.counted)
+    st = r.render(a.spp, a.bounces, counted=a.counted, flags=crt.RENDER_TIME_KERNELS if a.time_kernels else 0)
     print("rep %d: %.3f ms, %d rays, %.1f Mrays/s, %d launches, nodes/ray %.2f prims/ray %.2f" % (
         i, st.render_ms, st.rays, st.rays / st.render_ms / 1e3, st.kernel_launches,
         st.nodes_fetched / max(st.rays, 1), st.prims_tested / max(st.rays, 1)))

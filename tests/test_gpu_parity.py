@@ -105,6 +105,7 @@ def test_parked_rays_resume_bitwise(crt, rounds, parts, monkeypatch):
     monkeypatch.setenv("CRT_DRAIN_ROUNDS", str(rounds))
     monkeypatch.setenv("CRT_DRAIN_MIN_LIVE", "0")
     monkeypatch.setenv("CRT_WF_PARTS", str(parts))
+    monkeypatch.setenv("CRT_TAIL_LIVE", "0")             # no per-pixel tail kernel: every iteration is a wavefront one
     r = make_renderer(crt, sc, W, H, crt.MODE_WAVEFRONT)
     for _ in range(2):                                   # second frame: the pools are reused
         r.initialize(SEED, 0)
@@ -118,22 +119,64 @@ def test_parked_rays_resume_bitwise(crt, rounds, parts, monkeypatch):
 
 
 def test_parked_rays_full_size_default_settings(crt, monkeypatch):
-    """Default settings park rays only on long queues: a 2560x1440 frame, against a run with parking off."""
+    """Default settings park rays only on long queues and hand the last pixels of a part to k_wf_tail: a 2560x1440
+    frame, against a run with parking and the tail kernel off, and one with only the tail kernel off."""
     sc = crt.builtin_scene("cornell_blob")
     W, H = 2560, 1440
     out = []
-    for rounds in ("0", None):
-        if rounds is None:
-            monkeypatch.delenv("CRT_DRAIN_ROUNDS", raising=False)
-        else:
-            monkeypatch.setenv("CRT_DRAIN_ROUNDS", rounds)
+    for rounds, tail in (("0", "0"), (None, "0"), (None, None)):
+        for key, val in (("CRT_DRAIN_ROUNDS", rounds), ("CRT_TAIL_LIVE", tail)):
+            if val is None:
+                monkeypatch.delenv(key, raising=False)
+            else:
+                monkeypatch.setenv(key, val)
         r = make_renderer(crt, sc, W, H, crt.MODE_WAVEFRONT)
         st = r.render(3, 20)
-        out.append((r.accum().copy(), r.rng_state().copy(), int(st.rays)))
+        out.append((r.accum().copy(), r.rng_state().copy(), int(st.rays), r.image_rgba8().copy()))
         r.close()
-    assert np.array_equal(out[0][0].view(np.uint32), out[1][0].view(np.uint32))
-    assert np.array_equal(out[0][1], out[1][1])
-    assert out[0][2] == out[1][2]
+    for k in (1, 2):
+        assert np.array_equal(out[0][0].view(np.uint32), out[k][0].view(np.uint32))
+        assert np.array_equal(out[0][1], out[k][1])
+        assert out[0][2] == out[k][2]
+        assert np.array_equal(out[0][3], out[k][3])
+    sc.free()
+
+
+@pytest.mark.parametrize("tail_live,parts,rounds,iters,lanes_min", [(10**9, 2, None, 64, 1), (10**9, 1, 2, 1, 32), (6000, 2, 1, 3, 5),
+                                                                    (2500, 3, None, 7, 1), (300, 1, None, 1000, 2)])
+def test_tail_kernel_bitwise(crt, tail_live, parts, rounds, iters, lanes_min, monkeypatch):
+    """k_wf_tail finishes the pixels of a part whose queue has become short, one thread per pixel, entering the
+    megakernel's loop in the middle of a path (after a closing extend that also completes parked rays), in stages
+    of a bounded number of path segments with a write-back and a queue compaction between them. Whatever
+    the stage length, the lanes used per warp and the hand-over point (after the first batch; late, with a few hundred pixels left; with rays parked on every
+    launch before it), the frame equals the megakernel's bit for bit: accumulation, image, RNG state, ray count."""
+    sc = crt.builtin_scene("cornell_blob", 48)
+    W, H = 200, 120
+    r = make_renderer(crt, sc, W, H, crt.MODE_MEGAKERNEL)
+    st = r.render(7, 20)
+    want = (r.accum().copy(), r.image_rgba8().copy(), r.rng_state().copy(), int(st.rays))
+    r.close()
+    monkeypatch.setenv("CRT_TAIL_LIVE", str(tail_live))
+    monkeypatch.setenv("CRT_TAIL_ITERS", str(iters))          # path segments per pixel and stage, then write-back + compaction
+    monkeypatch.setenv("CRT_TAIL_LANES_MIN", str(lanes_min))  # lanes of a warp that take a pixel
+    monkeypatch.setenv("CRT_WF_PARTS", str(parts))
+    if rounds is not None:
+        monkeypatch.setenv("CRT_DRAIN_ROUNDS", str(rounds))
+        monkeypatch.setenv("CRT_DRAIN_MIN_LIVE", "0")
+    r = make_renderer(crt, sc, W, H, crt.MODE_WAVEFRONT)
+    for _ in range(2):
+        r.initialize(SEED, 0)
+        st = r.render(7, 20)
+        assert np.array_equal(want[0].view(np.uint32), r.accum().view(np.uint32))
+        assert np.array_equal(want[1], r.image_rgba8())
+        assert np.array_equal(want[2], r.rng_state())
+        assert want[3] == int(st.rays)
+    # passes accumulate across the hand-over as well
+    r.initialize(SEED, 0)
+    r.render(3, 20)
+    r.render(4, 20, flags=crt.RENDER_ACCUMULATE)
+    assert np.array_equal(want[0][..., :3].view(np.uint32), r.accum()[..., :3].view(np.uint32))
+    r.close()
     sc.free()
 
 
