@@ -119,7 +119,7 @@ typedef struct crt_config {
     int32_t height;
     int32_t device;        /* CUDA device ordinal                                       */
     int32_t mode;          /* CRT_MODE_*                                                */
-    int32_t bvh_leaf_max;  /* 0 = default (3)                                           */
+    int32_t bvh_leaf_max;  /* 0 = default (2), 1..3                                        */
     int32_t reserved[7];   /* must be zero                                              */
 } crt_config;
 

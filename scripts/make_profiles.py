@@ -38,7 +38,7 @@ want = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "la
 traffic = {}
 with open(os.path.join(P, out + "_ncu_kernels.txt"), "w") as f:
     f.write("# ncu --set full --clock-control none --import-source on, one launch each (steady state: launch #100 of a 64-spp frame, one part = half of the 3.69 M pixels per launch)\n")
-    for name, kern in (("extend", "k_wf_extend"), ("shade", "k_wf_shade"), ("mega", "k_render_mega")):
+    for name, kern in (("extend", "k_wf_extend"), ("shade", "k_wf_shade"), ("tail", "k_wf_tail"), ("mega", "k_render_mega")):
         rep = os.path.join(G, "%s_%s.ncu-rep" % (tag, name))
         if not os.path.exists(rep): continue
         txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout

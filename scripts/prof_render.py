@@ -15,10 +15,11 @@ ap.add_argument("--bounces", type=int, default=20)
 ap.add_argument("--reps", type=int, default=1)
 ap.add_argument("--counted", action="store_true")
 ap.add_argument("--time-kernels", action="store_true")
+ap.add_argument("--leaf-max", type=int, default=0)
 a = ap.parse_args()
 crt = importlib.import_module("raytracer-cuda_b200")
 sc = crt.builtin_scene(a.scene, a.param)
-r = crt.Renderer(a.width, a.height, mode=crt.MODE_WAVEFRONT if a.mode == "wavefront" else crt.MODE_MEGAKERNEL)
+r = crt.Renderer(a.width, a.height, mode=crt.MODE_WAVEFRONT if a.mode == "wavefront" else crt.MODE_MEGAKERNEL, bvh_leaf_max=a.leaf_max)
 r.set_scene(sc)
 r.update_camera(sc.camera)
 r.initialize(crt.REFERENCE_SEED, 0)

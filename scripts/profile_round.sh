@@ -9,6 +9,7 @@ P="python scripts/prof_render.py --spp 64"
 $P > gpurun_out/${TAG}_plain_wf.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:k_wf_extend -s 100 -c 1 -o gpurun_out/${TAG}_extend $P > gpurun_out/ncu_e.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_wf_shade -s 100 -c 1 -o gpurun_out/${TAG}_shade $P > gpurun_out/ncu_s.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_wf_tail -c 1 -o gpurun_out/${TAG}_tail $P > gpurun_out/ncu_t.log 2>&1
 P="python scripts/prof_render.py --spp 8 --mode megakernel"
 $P > gpurun_out/${TAG}_plain_mega.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:k_render_mega -c 1 -o gpurun_out/${TAG}_mega $P > gpurun_out/ncu_m.log 2>&1
