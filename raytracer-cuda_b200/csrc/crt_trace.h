@@ -49,10 +49,18 @@ CRT_HD float byte_f(uint32_t w, int i) { return (float)((w >> (8 * i)) & 0xffu);
 // adds it. The child-box bounds are then t = f*s + (o - 32768*s); the extra rounding of (o - 32768*s) is at
 // most 2^-9 |s| (1/512 of a grid step) and is covered by the conservative pad in visit_node.
 #define CRT_BYTE_MAGIC 32768.0f
+#if defined(__CUDACC__)
+static __device__ uint32_t g_byte_magic = 0x47000000u;   // see load_magic
+#endif
 #if defined(__CUDA_ARCH__)
-CRT_HD float byte_magic(uint32_t w, int i) { return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7504u | ((uint32_t)i << 4))); }
+// `magic` is 0x47000000 in a register whose value ptxas cannot know (load_magic reads it from a __device__ word):
+// given the literal, ptxas puts it into PRMT's one immediate slot and then spends a MOV per permute on bringing the
+// selector into a register (43 of the 296 instructions of a node visit in the SASS of the first version).
+CRT_HD float byte_magic(uint32_t w, int i, uint32_t magic) { return __uint_as_float(__byte_perm(w, magic, 0x7504u | ((uint32_t)i << 4))); }
+CRT_HD uint32_t load_magic() { return *(const volatile uint32_t*)&g_byte_magic; }
 #else
-CRT_HD float byte_magic(uint32_t w, int i) { return bits_f(0x47000000u | (((w >> (8 * i)) & 0xffu) << 8)); }
+CRT_HD float byte_magic(uint32_t w, int i, uint32_t) { return bits_f(0x47000000u | (((w >> (8 * i)) & 0xffu) << 8)); }
+CRT_HD uint32_t load_magic() { return 0x47000000u; }
 #endif
 
 // Primitive test against the interval [tmin, tmax] (both inclusive, Mesh.cuh:293 / Interval.cuh:33-35).
@@ -140,7 +148,7 @@ CRT_HD bool test_prim(const PrimRec* prims, uint32_t index, vec3 o, vec3 d, floa
 //      tg = primitive group (first primitive index, hit bits [23:0]). Hit bits are ordered so that the
 //      highest bit is the child the ray enters first (octant order).
 CRT_HD void visit_node(const WideNode* node, vec3 o, float idx, float idy, float idz, float tmin, float tmax, uint32_t octinv,
-                       uint32_t& ng_x, uint32_t& ng_y, uint32_t& tg_x, uint32_t& tg_y) {
+                       uint32_t& ng_x, uint32_t& ng_y, uint32_t& tg_x, uint32_t& tg_y, uint32_t mg) {
     const bool negx = idx < 0.f, negy = idy < 0.f, negz = idz < 0.f;
     const uint32_t octinv4 = octinv * 0x01010101u;
     const u4 n0 = ld_u4(&node->n0);
@@ -156,9 +164,11 @@ CRT_HD void visit_node(const WideNode* node, vec3 o, float idx, float idy, float
     const float ox = (px - o.x) * idx, oy = (py - o.y) * idy, oz = (pz - o.z) * idz;
     // conservative slack: covers the rounding of (p-o)*idir, of the per-child fma and of the magic-number shift
     const float eps = 4.76837158203125e-07f;   // 2^-21
-    const float padx = eps * (fabsf(ox) + 256.f * fabsf(sx)) + 0.00390625f * fabsf(sx);
-    const float pady = eps * (fabsf(oy) + 256.f * fabsf(sy)) + 0.00390625f * fabsf(sy);
-    const float padz = eps * (fabsf(oz) + 256.f * fabsf(sz)) + 0.00390625f * fabsf(sz);
+    // = eps * (|o| + 256 |s|) + |s| / 256, with the two |s| terms folded into one constant (exact: 2^-8 + 2^-13)
+    const float spad = 0.0040283203125f;
+    const float padx = eps * fabsf(ox) + spad * fabsf(sx);
+    const float pady = eps * fabsf(oy) + spad * fabsf(sy);
+    const float padz = eps * fabsf(oz) + spad * fabsf(sz);
     const float oxn = (ox - padx) - CRT_BYTE_MAGIC * sx, oxf = (ox + padx) - CRT_BYTE_MAGIC * sx;
     const float oyn = (oy - pady) - CRT_BYTE_MAGIC * sy, oyf = (oy + pady) - CRT_BYTE_MAGIC * sy;
     const float ozn = (oz - padz) - CRT_BYTE_MAGIC * sz, ozf = (oz + padz) - CRT_BYTE_MAGIC * sz;
@@ -182,9 +192,9 @@ CRT_HD void visit_node(const WideNode* node, vec3 o, float idx, float idy, float
 #pragma unroll
 #endif
         for (int j = 0; j < 4; j++) {
-            const float t0x = byte_magic(nearx, j) * sx + oxn, t1x = byte_magic(farx, j) * sx + oxf;
-            const float t0y = byte_magic(neary, j) * sy + oyn, t1y = byte_magic(fary, j) * sy + oyf;
-            const float t0z = byte_magic(nearz, j) * sz + ozn, t1z = byte_magic(farz, j) * sz + ozf;
+            const float t0x = byte_magic(nearx, j, mg) * sx + oxn, t1x = byte_magic(farx, j, mg) * sx + oxf;
+            const float t0y = byte_magic(neary, j, mg) * sy + oyn, t1y = byte_magic(fary, j, mg) * sy + oyf;
+            const float t0z = byte_magic(nearz, j, mg) * sz + ozn, t1z = byte_magic(farz, j, mg) * sz + ozf;
             const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
             const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
             if (cmin <= cmax) {
@@ -233,10 +243,12 @@ struct Traverser {
     HitRec rec;
     uint32_t ng_x, ng_y;   // node group: (first child index, hits[31:24] | imask[7:0])
     uint32_t octinv;
+    uint32_t mg;           // byte_magic's constant, see load_magic
     int sp;
 
     CRT_HD void begin(vec3 o_, vec3 d_, float tmin_, float tmax_) {
         o = o_; d = d_; tmin = tmin_;
+        mg = load_magic();
         rec.t = tmax_; rec.prim = 0u; rec.id = -1;
         // reciprocal direction with zero components nudged (box tests only; primitive tests use d)
         const float tiny = 1e-20f;
@@ -261,7 +273,7 @@ struct Traverser {
 #ifdef CRT_NODE_HOOK
             CRT_NODE_HOOK(base + rel);
 #endif
-            visit_node(sc.nodes + (base + rel), o, idx, idy, idz, tmin, rec.t, octinv, ng_x, ng_y, tg_x, tg_y);
+            visit_node(sc.nodes + (base + rel), o, idx, idy, idz, tmin, rec.t, octinv, ng_x, ng_y, tg_x, tg_y, mg);
         } else {
             tg_x = ng_x;
             tg_y = ng_y;

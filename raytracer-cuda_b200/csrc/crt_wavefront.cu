@@ -261,6 +261,7 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
     const int lane = threadIdx.x & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const float tmin = 0.001f;
+    const uint32_t magic = load_magic();   // byte_magic's constant, kept in a register for the whole launch
     uint32_t c_nodes = 0, c_prims = 0, c_rays = 0;
     TravStack st;
     vec3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
@@ -369,7 +370,7 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
             if (rest & 0xff000000u) { st.x[sp] = base; st.y[sp] = rest; sp++; }
             if (COUNT) c_nodes++;
             const float tmax = COOP ? __uint_as_float((uint32_t)(S.best[lane] >> 32)) : rec.t;
-            visit_node(scene.nodes + (base + rel), o, idx, idy, idz, tmin, tmax, octinv, ng_x, ng_y, tg_x, tg_y);
+            visit_node(scene.nodes + (base + rel), o, idx, idy, idz, tmin, tmax, octinv, ng_x, ng_y, tg_x, tg_y, magic);
         }
 
         __syncwarp();
