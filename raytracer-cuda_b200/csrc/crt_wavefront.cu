@@ -60,6 +60,7 @@ struct WavefrontState {
     cudaEvent_t ev_fork = nullptr;
     size_t n = 0;
     int blocks_extend = 0, blocks_shade = 0;
+    int extend_reverse = 1;          // env CRT_EXTEND_REVERSE: extend consumes the queue back to front (L2 reuse of what shade just wrote)
     int fetch_lanes = CRT_FETCH_LANES, postpone_lanes = CRT_POSTPONE_LANES, coop = 0, shade_persistent = 1;   // tuning knobs (env CRT_FETCH_LANES / CRT_POSTPONE_LANES)
     int drain_rounds = 4;            // env CRT_DRAIN_ROUNDS: rounds a warp keeps going after the queue ran out, then it suspends its rays (0 = never suspend)
     long long tail_live = 150000;    // env CRT_TAIL_LIVE: a part whose queue is at most this long is finished by k_wf_tail stages (0 = never)
@@ -251,7 +252,7 @@ struct WarpPool {
 template <bool COUNT, bool COOP>
 __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_wf_extend(SceneView scene, WfView w, uint32_t* queue, uint32_t* qcount, int cur,
                                                    unsigned long long* counters, int fetch_lanes, int drain_rounds,
-                                                   uint2* susp_out, const uint2* susp_in, int par) {
+                                                   uint2* susp_out, const uint2* susp_in, int par, int rev) {
     __shared__ WarpPool pools[COOP ? CRT_EXTEND_THREADS / 32 : 1];
     WarpPool& S = pools[COOP ? threadIdx.x >> 5 : 0];
     // work items: first the rays the previous launch parked (they are the long ones: started first, they have the
@@ -285,7 +286,10 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
             const uint2* r = susp_in + (size_t)i * CRT_SUSPEND_WORDS;
             bool take = !has_ray && i < count;
             if (take) {
-                pix = i < nres ? (r[0].x | PARKED_LANE) : queue[i - nres];
+                // the queue is consumed back to front: shade, which ran just before on this part, swept it front to back,
+                // so the path states it wrote last (still in L2) are the ones read first; the next shade starts at the
+                // front, where this kernel ends
+                pix = i < nres ? (r[0].x | PARKED_LANE) : queue[rev ? count - 1u - i : i - nres];
                 take = pix != QUEUE_DEAD;
             }
             float4 A = make_float4(0.f, 0.f, 0.f, 0.f), B = A;
@@ -700,6 +704,7 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&be, k_wf_extend<false, false>, CRT_EXTEND_THREADS, 0);
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade, 256, 0);
     if (const char* v = getenv("CRT_FETCH_LANES")) s->fetch_lanes = atoi(v);
+    if (const char* v = getenv("CRT_EXTEND_REVERSE")) s->extend_reverse = atoi(v);
     if (const char* v = getenv("CRT_COOP")) s->coop = atoi(v);
     if (const char* v = getenv("CRT_SHADE_PERSISTENT")) s->shade_persistent = atoi(v);
     if (const char* v = getenv("CRT_POSTPONE_LANES")) s->postpone_lanes = atoi(v);
@@ -806,7 +811,7 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                     if (timed) cudaEventRecord(ws->ev[ev_begin + 2 + 2 * p], st);
                     if (q.tail == 1) {
                         const int par = (int)(q.extend_launches++ & 1u);
-                        k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, 0, q.suspended[par], q.suspended[par ^ 1], par);
+                        k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, 0, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
                         q.tail = 2;
                         nl++;
                     }
@@ -830,9 +835,9 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                 const int drain = (suspend && (long long)q.live >= min_live) ? ws->drain_rounds : 0;
                 const int par = (int)(q.extend_launches++ & 1u);
                 if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p)], st);
-                if (counted) k_wf_extend<true, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par);
-                else if (ws->coop) k_wf_extend<false, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par);
-                else k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par);
+                if (counted) k_wf_extend<true, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
+                else if (ws->coop) k_wf_extend<false, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
+                else k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
                 if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p) + 1], st);
                 k_wf_shade<<<shade_grid, 256, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur, par);
                 if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p) + 2], st);

@@ -28,6 +28,8 @@ for i in range(a.reps):
     print("rep %d: %.3f ms, %d rays, %.1f Mrays/s, %d launches, nodes/ray %.2f prims/ray %.2f" % (
         i, st.render_ms, st.rays, st.rays / st.render_ms / 1e3, st.kernel_launches,
         st.nodes_fetched / max(st.rays, 1), st.prims_tested / max(st.rays, 1)))
+    if a.time_kernels:
+        print("   extend %.2f ms / %d launches, shade %.2f ms, tail %.2f ms" % (st.extend_ms, st.extend_launches, st.shade_ms, getattr(st, "tail_ms", 0.0)))
 bs = r.stats()
 print("bvh: %d nodes depth %d build %.2f ms; rng init %.2f ms" % (bs.bvh_nodes, bs.bvh_depth, bs.bvh_build_ms, bs.rng_init_ms))
 r.close()
