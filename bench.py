@@ -266,6 +266,12 @@ def main():
                 traffic, traffic_src = tj.get(kernel, {}).get("dram_bytes_per_launch"), tj.get(kernel, {}).get("source")
             except Exception:
                 pass
+        l2 = None   # L2-resident streaming-read bandwidth measured on this pool's B200 by scripts/l2_bw.cu
+        try:
+            l2j = json.load(open(os.path.join(ROOT, "profiles", "l2_peak.json")))
+            l2 = [pt["gbs"] for pt in l2j["points"] if pt["working_set_mb"] == 4][0]
+        except Exception:
+            pass
         roof = {"bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": (achieved / peaks["hbm_gbs"]) if achieved else None, "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": how + " (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)",
@@ -273,6 +279,8 @@ def main():
                 "algorithmic_bytes_per_launch": b_ray * k_run["rays"] / ext_launches,
                 "kernel_ms_per_launch": ext_ms / ext_launches, "kernel_launches_per_step": k_run["ext_launches"],
                 "kernel_share_of_step": ext_ms / k_run["ms"], "shade_ms_per_step": k_run["shade_ms"],
+                "l2_peak_gbs": l2, "frac_of_l2_peak": (achieved / l2) if (achieved and l2) else None,
+                "l2_peak_source": "profiles/l2_peak.json (scripts/l2_bw.cu, 4 MB working set, ld.global.cg)",
                 "note": "extend is instruction-issue bound, not DRAM bound: nodes and triangles (4.3 MB) are served from L1/L2, "
                         "so achieved/peak compares cache-served algorithmic bytes with the HBM copy peak; see DESIGN.md §3/§6"}
         cpu = None if args.no_cpu_baseline or world > 1 else cpu_baseline(crt, args)
