@@ -281,7 +281,7 @@ def main():
                 "kernel_share_of_step": ext_ms / k_run["ms"], "shade_ms_per_step": k_run["shade_ms"],
                 "l2_peak_gbs": l2, "frac_of_l2_peak": (achieved / l2) if (achieved and l2) else None,
                 "l2_peak_source": "profiles/l2_peak.json (scripts/l2_bw.cu, 4 MB working set, ld.global.cg)",
-                "note": "extend is instruction-issue bound, not DRAM bound: nodes and triangles (4.3 MB) are served from L1/L2, "
+                "note": "extend is bound by divergence and dependent-load latency, not DRAM: nodes and triangles (4.3 MB) are served from L1/L2, "
                         "so achieved/peak compares cache-served algorithmic bytes with the HBM copy peak; see DESIGN.md §3/§6"}
         cpu = None if args.no_cpu_baseline or world > 1 else cpu_baseline(crt, args)
         value = rays_all / dt / 1e6
