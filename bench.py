@@ -95,6 +95,15 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0}, "fallback"
 
 
+def which_config(args):
+    """The BASELINE.json config this run corresponds to (the default arguments are configs[1], the headline)."""
+    key = (args.scene, args.width, args.height, args.spp, args.bounces)
+    table = {("cornell", 256, 256, 16, 8): "BASELINE.json configs[0]", ("cornell_blob", 2560, 1440, 2000, 20): "BASELINE.json configs[1]",
+             ("spheres", 1200, 800, 500, 20): "BASELINE.json configs[2]", ("terrain", 2560, 1440, 256, 20): "BASELINE.json configs[3]",
+             ("cornell_blob", 1920, 1080, 1, 8): "BASELINE.json configs[4]"}
+    return table.get(key, "not a BASELINE.json config: a reduced or custom run")
+
+
 def cpu_baseline(crt, args):
     """The oracle (CPU port of the reference's algorithm) on the host cores, bounded sample."""
     import oracle_lib as ol
@@ -286,16 +295,17 @@ def main():
                 "kernel_share_of_step": ext_ms / k_run["ms"], "shade_ms_per_step": k_run["shade_ms"],
                 "l2_peak_gbs": l2, "frac_of_l2_peak": (achieved / l2) if (achieved and l2) else None,
                 "l2_peak_source": "profiles/l2_peak.json (scripts/l2_bw.cu, 4 MB working set, ld.global.cg)",
-                "note": "extend is bound by divergence and dependent-load latency, not DRAM: nodes and triangles (4.3 MB) are served from L1/L2, "
-                        "so achieved/peak compares cache-served algorithmic bytes with the HBM copy peak; see DESIGN.md §3/§6"}
+                "note": "extend is bound by divergence and dependent-load latency; where the scene fits the caches (all configs but the "
+                        "5 M-triangle terrain) nodes and triangles are served from L1/L2, so achieved/peak compares cache-served "
+                        "algorithmic bytes with the HBM copy peak; traffic is the ncu capture of the headline scene; see DESIGN.md §3/§6"}
         cpu = None if args.no_cpu_baseline or world > 1 else cpu_baseline(crt, args)
         value = rays_all / dt / 1e6
         line = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
-                "config": {"workload": "%s %dx%d %d spp %d bounces (BASELINE.json configs[1]); one step = one frame; spp sharded over "
+                "config": {"workload": "%s %dx%d %d spp %d bounces (%s); one step = one frame; spp sharded over "
                                        "ranks, one NCCL reduce of the float4 buffer per frame; per-step state %d MB > L2 (126 MB), so no L2 "
-                                       "flush between steps" % (args.scene, W, H, args.spp, args.bounces, (24 + 16 + 48 + 8) * W * H // 2 ** 20),
+                                       "flush between steps" % (args.scene, W, H, args.spp, args.bounces, which_config(args), (24 + 16 + 48 + 8) * W * H // 2 ** 20),
                            "mode": args.mode, "triangles": sc.num_triangles, "spheres": sc.num_spheres, "seed": SEED,
                            "bvh_nodes": int(build.bvh_nodes), "bvh_build_ms": build.bvh_build_ms, "rng_init_ms": build.rng_init_ms},
                 "frame_ms": dt / args.steps * 1e3, "rays_per_step": rays_all / args.steps,
