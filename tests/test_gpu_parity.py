@@ -487,3 +487,53 @@ def test_second_set_scene_replaces_the_first(crt):
     r.close()
     a.free()
     b.free()
+
+
+def _write_obj_room(tmp_path):
+    """A closed room with an emissive ceiling panel, a metal and a glass triangle pair: every material class of the
+    reference's MTL classification (SceneManager.h:222-247), polygons that need fan triangulation, negative indices."""
+    (tmp_path / "room.mtl").write_text(
+        "newmtl white\nKd 0.73 0.73 0.73\nnewmtl red\nKd 0.65 0.05 0.05\nnewmtl lamp\nKe 15 15 15\nKd 0 0 0\n"
+        "newmtl steel\nKd 0.8 0.8 0.9\nKs 0.5 0.5 0.5\nPr 0.1\nnewmtl glass\nKd 1 1 1\nd 0.3\nNi 1.5\n")
+    v = ["v -1 -1 -1", "v 1 -1 -1", "v 1 1 -1", "v -1 1 -1", "v -1 -1 1", "v 1 -1 1", "v 1 1 1", "v -1 1 1",
+         "v -0.3 0.99 -0.3", "v 0.3 0.99 -0.3", "v 0.3 0.99 0.3", "v -0.3 0.99 0.3",
+         "v -0.6 -1 -0.2", "v -0.1 -1 -0.2", "v -0.35 -0.2 -0.4", "v 0.2 -1 0.3", "v 0.7 -1 0.3", "v 0.45 -0.3 0.1"]
+    f = ["usemtl white", "f 1 2 6 5", "f 4 8 7 3", "f 1 4 3 2", "usemtl red", "f 1 5 8 4", "f 2 3 7 6",
+         "usemtl lamp", "f 9 10 11 12", "usemtl steel", "f 13 14 15", "usemtl glass", "f -3 -2 -1"]
+    (tmp_path / "room.obj").write_text("mtllib room.mtl\n" + "\n".join(v) + "\n" + "\n".join(f) + "\n")
+    return str(tmp_path / "room.obj")
+
+
+@pytest.mark.parametrize("mode", ["mega", "wave"])
+def test_obj_scene_matches_oracle(crt, tmp_path, mode):
+    """SURVEY.md 8(f) N1 through the render path: a scene that came in through crt_scene_load_obj (the reference's
+    loadObject rules + its two hard-coded spheres) renders to the oracle's bits."""
+    sc = crt.load_obj([_write_obj_room(tmp_path)])
+    assert sc.num_triangles == 14 and sc.num_spheres == 2
+    cam = crt.Camera()
+    cam.position[:] = (0.0, 0.0, 0.55)
+    cam.world_up[:] = (0.0, 1.0, 0.0)
+    cam.yaw_deg, cam.pitch_deg, cam.vfov_deg, cam.aspect, cam.aperture, cam.focus_dist = -90.0, 0.0, 70.0, 1.5, 0.01, 0.5
+    W, H, spp, bounces = 192, 128, 8, 12
+    osc = ol.OracleScene(sc.pointer())
+    r = crt.Renderer(W, H, mode=crt.MODE_MEGAKERNEL if mode == "mega" else crt.MODE_WAVEFRONT)
+    r.set_scene(sc)
+    r.update_camera(cam)
+    r.initialize(SEED, 0)
+    ids, t = r.primary_ids(SEED, 0)
+    oid, ot = osc.primary(cam, W, H, SEED)
+    assert np.array_equal(ids, oid)
+    assert np.array_equal(t.view(np.uint32), ot.view(np.uint32))
+    assert len(np.unique(ids)) >= 8          # walls, lamp, both triangles and the spheres are all in view
+    st = r.render(spp, bounces)
+    rad = r.accum()[..., :3] * np.float32(1.0 / spp)
+    orad, oimg, orays = osc.render(cam, W, H, spp, bounces, SEED)
+    assert int(st.rays) == int(orays)
+    exact = (rad.view(np.uint32) == orad.view(np.uint32)).all(axis=-1)
+    assert exact.mean() > 0.999, exact.mean()
+    assert (rel_err(rad, orad) <= 1e-4).all(axis=-1).mean() > 0.9995
+    assert (r.image_rgba8() != oimg).any(axis=-1).mean() < 5e-4
+    assert rad.max() > 1.0                   # the lamp is seen directly
+    r.close()
+    osc.close()
+    sc.free()
