@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define CRT_API_VERSION 1
+#define CRT_API_VERSION 2
 
 /* ---- error codes -------------------------------------------------------- */
 enum {
@@ -58,7 +58,8 @@ enum {
 
 typedef struct crt_material {
     int32_t type;          /* CRT_MAT_*                                            */
-    float   albedo[3];     /* Lambertian / Metal attenuation                        */
+    float   albedo[3];     /* Lambertian / Metal attenuation; finite and >= 0, else
+                              crt_set_scene fails with CRT_E_INVALID (-0.0 is stored as +0.0) */
     float   emission[3];   /* DiffuseLight radiance                                 */
     float   roughness;     /* Metal fuzz; clamped from above to 1 (Material.cuh:86) */
     float   ior;           /* Dielectric index of refraction                        */
@@ -162,7 +163,7 @@ typedef struct crt_stats {
     uint64_t nodes_fetched;
     uint64_t prims_tested;
     /* per-kernel-class device time of the last crt_render, filled with CRT_RENDER_TIME_KERNELS:
-     * wavefront: extend_ms = sum over k_wf_extend launches, shade_ms = k_wf_begin + k_wf_shade;
+     * wavefront: extend_ms = sum over k_wf_extend launches, shade_ms = sum over k_wf_shade launches;
      * megakernel: extend_ms = the one k_render_mega launch, shade_ms = 0 */
     float    extend_ms;
     float    shade_ms;
@@ -170,6 +171,10 @@ typedef struct crt_stats {
     uint32_t shade_launches;
     uint32_t bvh_giants;       /* primitives kept out of the BVH and tested by every ray (<= 4)  */
     float    tail_ms;          /* wavefront, with CRT_RENDER_TIME_KERNELS: the closing extend + k_wf_tail launches   */
+    float    begin_ms;         /* wavefront, with CRT_RENDER_TIME_KERNELS: k_wf_begin                                 */
+    float    compact_ms;       /* wavefront, with CRT_RENDER_TIME_KERNELS: the k_compact_* triples                    */
+    uint32_t host_syncs;       /* blocking stream synchronisations inside the last crt_render (queue-length read-backs) */
+    uint32_t iterations;       /* wavefront iterations (extend + shade per part) of the last crt_render               */
     uint64_t reserved[1];
 } crt_stats;
 
@@ -256,8 +261,9 @@ int crt_get_stream(crt_ctx* ctx, void** out_stream);
 
 /* Make the context launch on the caller's stream (cudaStream_t) instead of its own, so that the caller's
  * events and collectives (e.g. the multi-GPU reduce of the accumulation buffer) order with the render
- * without extra synchronisation. NULL restores the context's own stream. The legacy default stream of the
- * reference (src/CUDARenderer.cuh:57) is what this generalises. */
+ * without extra synchronisation. NULL restores the context's own stream; that also means the legacy default
+ * stream (handle 0, what the reference launches on, src/CUDARenderer.cuh:57) cannot be selected: pass a stream
+ * the caller created. */
 int crt_set_stream(crt_ctx* ctx, void* stream);
 
 /* ---- built-in procedural scenes (BASELINE.json configs; assets/ is absent upstream) ---

@@ -219,7 +219,9 @@ public:
         cfg.width = width; cfg.height = height; cfg.device = device; cfg.mode = mode;
         const int rc = crt_create(&m_Ctx, &cfg);
         if (rc != CRT_OK) {
-            const std::string why = m_Ctx ? crt_last_error(m_Ctx) : errorName(rc);
+            // crt_create leaves *out_ctx null on failure; its detail message is kept under the null context
+            std::string why = crt_last_error(m_Ctx);
+            if (why.empty()) why = errorName(rc);
             crt_destroy(m_Ctx);
             m_Ctx = nullptr;
             throw std::runtime_error("CUDA error: " + why + " (code " + std::to_string(rc) + ")");

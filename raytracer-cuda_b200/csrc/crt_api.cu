@@ -5,6 +5,7 @@
 // No CPU fallback: every entry point that needs the GPU fails with CRT_E_NO_DEVICE / CRT_E_CUDA.
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -169,6 +170,26 @@ int crt_set_scene(crt_ctx* ctx, const crt_scene* sc) {
     if (sc->num_materials && !sc->materials) return fail(ctx, CRT_E_INVALID, "crt_set_scene: null materials");
     for (size_t i = 0; i < (size_t)3 * T; i++)
         if (sc->indices[i] >= sc->num_vertices) return fail(ctx, CRT_E_INVALID, "crt_set_scene: vertex index out of range");
+    // Attenuations must be finite and >= 0: the path throughput is their product, and the wavefront kernels keep a
+    // per-pixel flag in the sign bit of throughput.x (crt_wavefront.cu, PARKED_SIGN). A negative or NaN albedo has no
+    // physical meaning; -0.0 is stored as +0.0 (same radiance bits: only products with 0 are affected).
+    std::vector<MatRec> mats;
+    try {
+        mats.reserve(sc->num_materials);
+        for (uint32_t i = 0; i < sc->num_materials; i++) {
+            MatRec m = make_mat_record(sc->materials[i]);
+            if (m.type == CRT_MAT_LAMBERTIAN || m.type == CRT_MAT_METAL) {
+                float* c[3] = {&m.a.x, &m.a.y, &m.a.z};
+                for (float* v : c) {
+                    if (!(*v >= 0.f) || !std::isfinite(*v)) return fail(ctx, CRT_E_INVALID, "crt_set_scene: albedo components must be finite and >= 0");
+                    *v += 0.f;   // -0 -> +0
+                }
+            }
+            mats.push_back(m);
+        }
+    } catch (const std::bad_alloc&) {
+        return fail(ctx, CRT_E_NOMEM, "crt_set_scene: out of host memory");
+    }
     CU(cudaSetDevice(ctx->cfg.device));
     CU(cudaStreamSynchronize(ctx->stream));
     free_scene(ctx);
@@ -187,8 +208,6 @@ int crt_set_scene(crt_ctx* ctx, const crt_scene* sc) {
         CU(cudaMemcpyAsync(ctx->d_sph, sc->spheres, (size_t)S * 4 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaMemcpyAsync(ctx->d_sphmat, sc->sphere_material, (size_t)S * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
     }
-    std::vector<MatRec> mats;
-    for (uint32_t i = 0; i < sc->num_materials; i++) mats.push_back(make_mat_record(sc->materials[i]));
     ctx->num_mats = sc->num_materials;
     CU(cudaMalloc(&ctx->d_mats, (mats.size() ? mats.size() : 1) * sizeof(MatRec)));
     if (!mats.empty()) CU(cudaMemcpyAsync(ctx->d_mats, mats.data(), mats.size() * sizeof(MatRec), cudaMemcpyHostToDevice, ctx->stream));
@@ -248,8 +267,9 @@ static int render_impl(crt_ctx* ctx, const crt_render_params* p, bool counted) {
     uint32_t launches = 0;
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
     KernelTimes kt;
+    bool incomplete = false;
     if (mega) CU(launch_render_mega(a, counted, ctx->num_sms, ctx->stream, &launches));
-    else CU(launch_render_wavefront(ctx->wf, a, counted, ctx->num_sms, ctx->stream, &launches, &kt));
+    else CU(launch_render_wavefront(ctx->wf, a, counted, ctx->num_sms, ctx->stream, &launches, &kt, &incomplete));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     unsigned long long c[4] = {0, 0, 0, 0};
     CU(cudaMemcpyAsync(c, ctx->fb.counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
@@ -264,6 +284,8 @@ static int render_impl(crt_ctx* ctx, const crt_render_params* p, bool counted) {
     if (mega) { kt.extend_ms = ctx->stats.render_ms; kt.extend_launches = 1; }
     ctx->stats.extend_ms = kt.extend_ms; ctx->stats.shade_ms = kt.shade_ms; ctx->stats.tail_ms = kt.tail_ms;
     ctx->stats.extend_launches = kt.extend_launches; ctx->stats.shade_launches = kt.shade_launches;
+    ctx->stats.begin_ms = kt.begin_ms; ctx->stats.compact_ms = kt.compact_ms; ctx->stats.host_syncs = kt.host_syncs + 1u; ctx->stats.iterations = kt.iterations;
+    if (incomplete) return fail(ctx, CRT_E_LIMIT, "crt_render: iteration bound reached with pixels still unfinished (frame incomplete)");
     return CRT_OK;
 }
 

@@ -26,9 +26,27 @@ struct WideBvh {
     uint32_t ploc_rounds = 0;
 };
 
-// Returns 0 on success, CRT_E_* otherwise. `in` points into exec memory.
+// Temporaries of one build: released on every way out of build_wide_bvh (the early error returns included).
+template <class Exec>
+struct BuildScratch {
+    Exec& ex;
+    void* ptr[32];
+    int n = 0;
+    explicit BuildScratch(Exec& e) : ex(e) {}
+    ~BuildScratch() { while (n > 0) ex.release(ptr[--n]); }
+    template <class T> T* alloc(size_t count) {
+        T* p = n < 32 ? ex.template alloc<T>(count) : nullptr;
+        if (p) ptr[n++] = p;
+        return p;
+    }
+    BuildScratch(const BuildScratch&) = delete;
+    BuildScratch& operator=(const BuildScratch&) = delete;
+};
+
+// Returns 0 on success, CRT_E_* otherwise (then `out` holds no allocation). `in` points into exec memory.
 template <class Exec>
 int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& out) {
+    BuildScratch<Exec> tmp(ex);
     const uint32_t Nall = in.num_triangles + in.num_spheres;
     if (Nall == 0) return CRT_E_INVALID;
     if (Nall > 0x07ffffffu) return CRT_E_LIMIT;   // primitive record indices travel in 27 bits
@@ -36,24 +54,24 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
     if (leaf_max > 3) leaf_max = 3;
     const uint32_t N_alloc = Nall;
 
-    f4* plo = ex.template alloc<f4>(N_alloc);
-    f4* phi = ex.template alloc<f4>(N_alloc);
-    int32_t* cbounds = ex.template alloc<int32_t>(6);
-    uint64_t* keys = ex.template alloc<uint64_t>(N_alloc);
-    uint64_t* keys_tmp = ex.template alloc<uint64_t>(N_alloc);
-    uint32_t* vals = ex.template alloc<uint32_t>(N_alloc);
-    uint32_t* vals_tmp = ex.template alloc<uint32_t>(N_alloc);
+    f4* plo = tmp.template alloc<f4>(N_alloc);
+    f4* phi = tmp.template alloc<f4>(N_alloc);
+    int32_t* cbounds = tmp.template alloc<int32_t>(6);
+    uint64_t* keys = tmp.template alloc<uint64_t>(N_alloc);
+    uint64_t* keys_tmp = tmp.template alloc<uint64_t>(N_alloc);
+    uint32_t* vals = tmp.template alloc<uint32_t>(N_alloc);
+    uint32_t* vals_tmp = tmp.template alloc<uint32_t>(N_alloc);
     const size_t nb = (size_t)2 * N_alloc;   // 2N-1 binary nodes
-    f4* blo = ex.template alloc<f4>(nb);
-    f4* bhi = ex.template alloc<f4>(nb);
-    uint32_t* bcount = ex.template alloc<uint32_t>(nb);
-    uint32_t* cl_a = ex.template alloc<uint32_t>(N_alloc);
-    uint32_t* cl_b = ex.template alloc<uint32_t>(N_alloc);
-    uint32_t* nearest = ex.template alloc<uint32_t>(N_alloc);
-    uint32_t* merged = ex.template alloc<uint32_t>(N_alloc);
-    uint32_t* flags = ex.template alloc<uint32_t>(N_alloc);
-    uint32_t* pos = ex.template alloc<uint32_t>(N_alloc);
-    uint32_t* counters = ex.template alloc<uint32_t>(4);   // [0] wide nodes [1] prims [2] binary nodes [3] ploc total
+    f4* blo = tmp.template alloc<f4>(nb);
+    f4* bhi = tmp.template alloc<f4>(nb);
+    uint32_t* bcount = tmp.template alloc<uint32_t>(nb);
+    uint32_t* cl_a = tmp.template alloc<uint32_t>(N_alloc);
+    uint32_t* cl_b = tmp.template alloc<uint32_t>(N_alloc);
+    uint32_t* nearest = tmp.template alloc<uint32_t>(N_alloc);
+    uint32_t* merged = tmp.template alloc<uint32_t>(N_alloc);
+    uint32_t* flags = tmp.template alloc<uint32_t>(N_alloc);
+    uint32_t* pos = tmp.template alloc<uint32_t>(N_alloc);
+    uint32_t* counters = tmp.template alloc<uint32_t>(4);   // [0] wide nodes [1] prims [2] binary nodes [3] ploc total
     if (!plo || !phi || !cbounds || !keys || !keys_tmp || !vals || !vals_tmp || !blo || !bhi || !bcount || !cl_a || !cl_b ||
         !nearest || !merged || !flags || !pos || !counters)
         return CRT_E_NOMEM;
@@ -70,7 +88,7 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
     giants.count = 0;
     for (int k = 0; k < CRT_MAX_GIANTS; k++) giants.id[k] = 0xffffffffu;
     {
-        unsigned long long* key = ex.template alloc<unsigned long long>(1);
+        unsigned long long* key = tmp.template alloc<unsigned long long>(1);
         if (!key) return CRT_E_NOMEM;
         // candidates: the CRT_MAX_GIANTS largest primitives, largest first; accept the longest prefix whose
         // smallest member is still CRT_GIANT_RATIO x larger than the bounds of everything outside the prefix
@@ -105,7 +123,6 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
             else if (!(cand_extent > rest)) break;                      // candidates no larger than the rest: no longer prefix can qualify
         }
         giants = accepted;
-        ex.release(key);
     }
     const uint32_t N = Nall - giants.count;   // primitives inside the BVH
     const int n0 = (int)N;
@@ -164,10 +181,15 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
     // 4. collapse. Every wide node stands for a distinct binary node (an inner one, or a small subtree that
     // was given its own frame, CollapseFn), of which there are 2N-1; N prim records.
     const uint32_t node_cap = 2 * N;
+    auto fail_out = [&](int code) {
+        ex.release(out.nodes); ex.release(out.prims);
+        out = WideBvh();
+        return code;
+    };
     out.nodes = ex.template alloc<WideNode>(node_cap);
     out.prims = ex.template alloc<PrimRec>(Nall);
-    uint32_t* wide_bnode = ex.template alloc<uint32_t>(node_cap);
-    if (!out.nodes || !out.prims || !wide_bnode) return CRT_E_NOMEM;
+    uint32_t* wide_bnode = tmp.template alloc<uint32_t>(node_cap);
+    if (!out.nodes || !out.prims || !wide_bnode) return fail_out(CRT_E_NOMEM);
     ex.upload(wide_bnode, &root, sizeof(uint32_t));
     uint32_t begin = 0, end = 1, depth = 0;
     while (begin < end) {
@@ -181,18 +203,13 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
         end = c[0];
         out.num_prims = c[1];
         depth++;
-        if (end > node_cap) return CRT_E_LIMIT;
+        if (end > node_cap) return fail_out(CRT_E_LIMIT);   // cannot happen: every wide node stands for a distinct binary node (<= 2N-1)
     }
     out.num_nodes = end;
     out.depth = depth;
     out.ploc_rounds = rounds;
 
-    ex.release(wide_bnode);
-    ex.release(counters); ex.release(pos); ex.release(flags); ex.release(merged); ex.release(nearest);
-    ex.release(cl_b); ex.release(cl_a); ex.release(bcount); ex.release(bhi); ex.release(blo);
-    ex.release(vals_tmp); ex.release(vals); ex.release(keys_tmp); ex.release(keys);
-    ex.release(cbounds); ex.release(phi); ex.release(plo);
-    if (out.num_prims != N) return CRT_E_CUDA;
+    if (out.num_prims != N) return fail_out(CRT_E_CUDA);
     // giants: records appended after the BVH's
     out.giant_base = N;
     out.giant_count = giants.count;

@@ -31,9 +31,17 @@ crt_scene* scene_holder_release(SceneData&& data) {
 }
 }  // namespace crt
 
+// No exception crosses the C boundary: a std::bad_alloc from the host-side staging vectors (a 2560x1440 checkpoint
+// stages ~150 MB) becomes CRT_E_NOMEM, anything else CRT_E_INVALID.
+#define CRT_TRY try {
+#define CRT_CATCH(ctx, what)                                                                            \
+    } catch (const std::bad_alloc&) { return crt_ctx_fail_(ctx, CRT_E_NOMEM, what ": out of host memory");  \
+    } catch (...) { return crt_ctx_fail_(ctx, CRT_E_INVALID, what ": unexpected C++ exception"); }
+
 extern "C" {
 
 int crt_scene_builtin(const char* name, int32_t param, crt_scene** out_scene, crt_camera* out_cam) {
+    CRT_TRY
     if (!name || !out_scene) return CRT_E_INVALID;
     *out_scene = nullptr;
     crt::SceneData data;
@@ -44,6 +52,7 @@ int crt_scene_builtin(const char* name, int32_t param, crt_scene** out_scene, cr
     *out_scene = v;
     if (out_cam) *out_cam = cam;
     return CRT_OK;
+    CRT_CATCH(nullptr, "crt_scene_builtin")
 }
 
 void crt_scene_free(crt_scene* scene) {
@@ -54,6 +63,7 @@ void crt_scene_free(crt_scene* scene) {
 // Replaces WindowManager::drawFrame's D2H copy + flipVertically (reference:
 // CudaRayTracer/src/WindowManager.h:79-93): the file is written top row first.
 int crt_write_ppm(crt_ctx* ctx, const char* path) {
+    CRT_TRY
     int w = 0, h = 0;
     if (!ctx || !path || crt_ctx_size_(ctx, &w, &h) != CRT_OK) return CRT_E_INVALID;
     std::vector<unsigned char> img((size_t)w * h * 4);
@@ -70,9 +80,11 @@ int crt_write_ppm(crt_ctx* ctx, const char* path) {
     bool ok = !ferror(f);
     fclose(f);
     return ok ? CRT_OK : crt_ctx_fail_(ctx, CRT_E_IO, "crt_write_ppm: write failed");
+    CRT_CATCH(ctx, "crt_write_ppm")
 }
 
 int crt_write_pfm(crt_ctx* ctx, const char* path) {
+    CRT_TRY
     int w = 0, h = 0;
     if (!ctx || !path || crt_ctx_size_(ctx, &w, &h) != CRT_OK) return CRT_E_INVALID;
     std::vector<float> acc((size_t)w * h * 4);
@@ -93,11 +105,13 @@ int crt_write_pfm(crt_ctx* ctx, const char* path) {
     bool ok = !ferror(f);
     fclose(f);
     return ok ? CRT_OK : crt_ctx_fail_(ctx, CRT_E_IO, "crt_write_pfm: write failed");
+    CRT_CATCH(ctx, "crt_write_pfm")
 }
 
 // Checkpoint file: "CRTCKPT1", width, height (int32), accumulation buffer (w*h*4 float),
 // RNG planes (6*w*h uint32). The reference persists nothing.
 int crt_checkpoint_save(crt_ctx* ctx, const char* path) {
+    CRT_TRY
     int w = 0, h = 0;
     if (!ctx || !path || crt_ctx_size_(ctx, &w, &h) != CRT_OK) return CRT_E_INVALID;
     const size_t n = (size_t)w * h;
@@ -116,9 +130,11 @@ int crt_checkpoint_save(crt_ctx* ctx, const char* path) {
     bool ok = !ferror(f);
     fclose(f);
     return ok ? CRT_OK : crt_ctx_fail_(ctx, CRT_E_IO, "crt_checkpoint_save: write failed");
+    CRT_CATCH(ctx, "crt_checkpoint_save")
 }
 
 int crt_checkpoint_load(crt_ctx* ctx, const char* path) {
+    CRT_TRY
     int w = 0, h = 0;
     if (!ctx || !path || crt_ctx_size_(ctx, &w, &h) != CRT_OK) return CRT_E_INVALID;
     FILE* f = fopen(path, "rb");
@@ -136,6 +152,7 @@ int crt_checkpoint_load(crt_ctx* ctx, const char* path) {
     int rc = crt_set_accum(ctx, acc.data());
     if (rc == CRT_OK) rc = crt_set_rng_state(ctx, rng.data());
     return rc;
+    CRT_CATCH(ctx, "crt_checkpoint_load")
 }
 
 }  // extern "C"

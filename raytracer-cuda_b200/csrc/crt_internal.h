@@ -26,8 +26,9 @@ struct RenderArgs {
 };
 
 struct KernelTimes {
-    float extend_ms = 0.f, shade_ms = 0.f, tail_ms = 0.f;
+    float extend_ms = 0.f, shade_ms = 0.f, tail_ms = 0.f, begin_ms = 0.f, compact_ms = 0.f;
     uint32_t extend_launches = 0, shade_launches = 0;
+    uint32_t host_syncs = 0, compactions = 0, iterations = 0;   // blocking stream synchronisations / queue compactions / wavefront iterations of the frame
 };
 
 // crt_render.cu — every launcher enqueues on `stream` and returns the launch error (no sync).
@@ -43,6 +44,6 @@ struct WavefrontState;   // persistent path state, owned by the context
 cudaError_t wavefront_create(WavefrontState** out, int width, int height);
 void wavefront_destroy(WavefrontState* s);
 cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, bool counted, int num_sms, cudaStream_t stream,
-                                    uint32_t* launches, KernelTimes* times);
+                                    uint32_t* launches, KernelTimes* times, bool* incomplete);
 
 }  // namespace crt

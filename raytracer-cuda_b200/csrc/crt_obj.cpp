@@ -21,6 +21,7 @@
 #include <cstring>
 #include <fstream>
 #include <map>
+#include <new>
 #include <set>
 #include <sstream>
 #include <string>
@@ -165,6 +166,7 @@ extern "C" int crt_scene_load_obj(const char* const* paths, int32_t num_paths, i
     auto set_err = [&](const std::string& m) { if (err_buf && err_len) { snprintf(err_buf, err_len, "%s", m.c_str()); } };
     if (!paths || num_paths <= 0 || !out_scene) { set_err("crt_scene_load_obj: bad arguments"); return CRT_E_INVALID; }
     *out_scene = nullptr;
+    try {   // no exception crosses the C boundary
     std::vector<FileMesh> meshes;
     std::vector<crt_material> materials;
     for (int i = 0; i < num_paths; i++) {
@@ -213,4 +215,11 @@ extern "C" int crt_scene_load_obj(const char* const* paths, int32_t num_paths, i
     if (!v) { set_err("out of memory"); return CRT_E_NOMEM; }
     *out_scene = v;
     return CRT_OK;
+    } catch (const std::bad_alloc&) {
+        set_err("crt_scene_load_obj: out of host memory");
+        return CRT_E_NOMEM;
+    } catch (...) {
+        set_err("crt_scene_load_obj: unexpected C++ exception");
+        return CRT_E_INVALID;
+    }
 }

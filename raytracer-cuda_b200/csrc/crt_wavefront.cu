@@ -69,7 +69,7 @@ struct WavefrontState {
     int tail_blocks = 4;             // resident k_wf_tail CTAs per SM (occupancy query)
     int tail_shade_lanes = 8;        // env CRT_TAIL_SHADE_LANES: of 32; lanes that have to be waiting before a tail warp runs its shade step
     long long drain_min_live = -1;   // env CRT_DRAIN_MIN_LIVE: suspend only while the part's queue is at least this long (-1 = one ray per extend thread)
-    cudaEvent_t ev[3 * 16 * CRT_WF_MAX_PARTS + 2 + 2 * CRT_WF_MAX_PARTS] = {};   // CRT_RENDER_TIME_KERNELS: begin pair + 3 events per (iteration, part) of a batch
+    cudaEvent_t ev[3 * 16 * CRT_WF_MAX_PARTS + 2 + 4 * CRT_WF_MAX_PARTS] = {};   // CRT_RENDER_TIME_KERNELS: 3 events per (iteration, part) of a batch, begin pair, tail pair and compaction pair per part
 };
 
 struct WfView {
@@ -246,6 +246,9 @@ struct WarpPool {
 #ifndef CRT_EXTEND_THREADS
 #define CRT_EXTEND_THREADS 256
 #endif
+#ifndef CRT_SMEM_STACK
+#define CRT_SMEM_STACK 0   // entries of the traversal stack kept in shared memory (0 = all in local memory); see DESIGN.md 3.2
+#endif
 #ifndef CRT_EXTEND_MIN_BLOCKS
 #define CRT_EXTEND_MIN_BLOCKS (1024 / CRT_EXTEND_THREADS)
 #endif
@@ -264,7 +267,25 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
     const float tmin = 0.001f;
     const uint32_t magic = load_magic();   // byte_magic's constant, kept in a register for the whole launch
     uint32_t c_nodes = 0, c_prims = 0, c_rays = 0;
+    // Traversal stack: the first CRT_SMEM_STACK entries live in shared memory ([entry][thread]: conflict-free 8-byte
+    // accesses), deeper ones spill to the thread's local-memory array. A ray of the headline scene makes 2.5 node
+    // visits, so its stack seldom passes 3 entries; the deep entries are for the 5 M-triangle tree.
+#if CRT_SMEM_STACK > 0
+    __shared__ uint2 sstack[CRT_SMEM_STACK][CRT_EXTEND_THREADS];
+    uint32_t lx[CRT_STACK_ENTRIES - CRT_SMEM_STACK], ly[CRT_STACK_ENTRIES - CRT_SMEM_STACK];
+    auto st_set = [&](int k, uint32_t x, uint32_t y) {
+        if (k < CRT_SMEM_STACK) sstack[k][threadIdx.x] = make_uint2(x, y);
+        else { lx[k - CRT_SMEM_STACK] = x; ly[k - CRT_SMEM_STACK] = y; }
+    };
+    auto st_get = [&](int k) -> uint2 {
+        if (k < CRT_SMEM_STACK) return sstack[k][threadIdx.x];
+        return make_uint2(lx[k - CRT_SMEM_STACK], ly[k - CRT_SMEM_STACK]);
+    };
+#else
     TravStack st;
+    auto st_set = [&](int k, uint32_t x, uint32_t y) { st.x[k] = x; st.y[k] = y; };
+    auto st_get = [&](int k) -> uint2 { return make_uint2(st.x[k], st.y[k]); };
+#endif
     vec3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
     HitRec rec;
     rec.t = INFINITY; rec.prim = 0u; rec.id = -1;
@@ -314,7 +335,7 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
                     const uint2 r0 = r[0], r1 = r[1], r2 = r[2], r3 = r[3];
                     rec.t = __uint_as_float(r1.x); rec.prim = r1.y; rec.id = (int32_t)r2.x;
                     sp = (int)r0.y; ng_x = r3.x; ng_y = r3.y;
-                    for (int k = 0; k < sp; k++) { const uint2 e = r[4 + k]; st.x[k] = e.x; st.y[k] = e.y; }
+                    for (int k = 0; k < sp; k++) { const uint2 e = r[4 + k]; st_set(k, e.x, e.y); }
                 } else {
                 sp = 0; ng_x = 0u; ng_y = 0x80000000u;
                 if (COOP) {
@@ -355,7 +376,7 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
                 r[1] = make_uint2(__float_as_uint(rec.t), rec.prim);
                 r[2] = make_uint2((uint32_t)rec.id, 0u);
                 r[3] = make_uint2(ng_x, ng_y);
-                for (int k = 0; k < sp; k++) r[4 + k] = make_uint2(st.x[k], st.y[k]);
+                for (int k = 0; k < sp; k++) r[4 + k] = st_get(k);
                 w.C[pix & PIXEL_MASK].x = PARKED_T;
                 if (!(pix & PARKED_LANE)) {
                     uint32_t* aw = reinterpret_cast<uint32_t*>(&w.A[pix].w);
@@ -371,7 +392,7 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
             const uint32_t base = ng_x;
             uint32_t rest = ng_y;
             const uint32_t rel = next_child(rest, octinv);
-            if (rest & 0xff000000u) { st.x[sp] = base; st.y[sp] = rest; sp++; }
+            if (rest & 0xff000000u) { st_set(sp, base, rest); sp++; }
             if (COUNT) c_nodes++;
             const float tmax = COOP ? __uint_as_float((uint32_t)(S.best[lane] >> 32)) : rec.t;
             visit_node(scene.nodes + (base + rel), o, idx, idy, idz, tmin, tmax, octinv, ng_x, ng_y, tg_x, tg_y, magic);
@@ -454,8 +475,9 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
                 has_ray = false;
             } else {
                 sp--;
-                ng_x = st.x[sp];
-                ng_y = st.y[sp];
+                const uint2 e = st_get(sp);
+                ng_x = e.x;
+                ng_y = e.y;
             }
         }
     }
@@ -496,31 +518,35 @@ __device__ __forceinline__ bool shade_step(const RenderArgs& a, uint32_t pix, ve
         result = v_mul(thr, background(d));
         ended = true;
     }
-    if (!ended) bounce++;
-    // Finish / regenerate / Russian roulette, in the megakernel's order: a path that ends
-    // adds its radiance and the pixel's next sample starts at once; RR is drawn before the
-    // next closest-hit query whenever bounce >= min_bounces (CUDAKernels.h:113-121).
+    // Russian roulette / finish / regenerate, in the megakernel's order: RR is drawn before the next closest-hit
+    // query whenever bounce >= min_bounces (CUDAKernels.h:113-121); a path that ends adds its radiance and the
+    // pixel's next sample starts at once. The continuing lanes draw RR FIRST so that every way a path can end
+    // (emission, sky, roulette, bounce limit) reaches the "path ended" block together: the block (accumulator
+    // load, camera ray with its rejection loop) is issued once per warp, not once per reason. A fresh path starts
+    // at bounce 0 < min_bounces (crt_render enforces min_bounces >= 1 and max_bounces >= 1), so it draws no RR here.
+    if (!ended) {
+        bounce++;
+        if (bounce >= a.rc.max_bounces) {
+            ended = true;                                             // exhausted: black
+        } else if (bounce >= a.rc.min_bounces) {
+            const float p = fminf(fmaxf(thr.x, fmaxf(thr.y, thr.z)), a.rc.rr_max_prob);
+            if (rng_uniform(rng) > p) ended = true;
+            else thr = v_scale(thr, f_rcp(p));
+        }
+    }
     keep = true;
-    while (true) {
-        if (ended) {
-            if (!touched) { acc = a.fb.accum[pix]; touched = true; }
-            acc.x = f_add(acc.x, result.x); acc.y = f_add(acc.y, result.y); acc.z = f_add(acc.z, result.z);
-            sample++;
-            if (sample >= a.rc.spp) { keep = false; break; }
+    if (ended) {
+        if (!touched) { acc = a.fb.accum[pix]; touched = true; }
+        acc.x = f_add(acc.x, result.x); acc.y = f_add(acc.y, result.y); acc.z = f_add(acc.z, result.z);
+        sample++;
+        if (sample >= a.rc.spp) {
+            keep = false;
+        } else {
             const int x = (int)(pix % (uint32_t)a.rc.width), y = (int)(pix / (uint32_t)a.rc.width);
             camera_ray(a.cam, x, y, a.rc.width, a.rc.height, rng, o, d);
             thr = mk3(1.f, 1.f, 1.f);
             bounce = 0;
-            result = mk3(0.f, 0.f, 0.f);
-            ended = false;
         }
-        if (bounce >= a.rc.max_bounces) { ended = true; continue; }   // exhausted: black
-        if (bounce >= a.rc.min_bounces) {
-            const float p = fminf(fmaxf(thr.x, fmaxf(thr.y, thr.z)), a.rc.rr_max_prob);
-            if (rng_uniform(rng) > p) { ended = true; continue; }
-            thr = v_scale(thr, f_rcp(p));
-        }
-        break;
     }
     return keep;
 }
@@ -741,7 +767,8 @@ void wavefront_destroy(WavefrontState* s) {
 }
 
 cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, bool counted, int num_sms, cudaStream_t stream,
-                                    uint32_t* launches, KernelTimes* times) {
+                                    uint32_t* launches, KernelTimes* times, bool* incomplete) {
+    if (incomplete) *incomplete = false;
     if (!ws) return cudaErrorInvalidValue;
     WfView w;
     w.A = ws->A; w.B = ws->B; w.C = ws->C;
@@ -752,7 +779,7 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
     const int parts = ws->parts;
     const int ev_begin = 3 * batch * CRT_WF_MAX_PARTS;
     if (timed && !ws->ev[0])
-        for (int i = 0; i < ev_begin + 2 + 2 * CRT_WF_MAX_PARTS && e == cudaSuccess; i++) e = cudaEventCreate(&ws->ev[i]);
+        for (int i = 0; i < ev_begin + 2 + 4 * CRT_WF_MAX_PARTS && e == cudaSuccess; i++) e = cudaEventCreate(&ws->ev[i]);
     if (e != cudaSuccess) return e;
     const size_t tiles_all = (ws->n + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE;
     // rays are parked (see k_wf_extend) only by the plain kernel and only while the queue is longer than one
@@ -775,7 +802,7 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         bq.queue[p] = q.queue[0]; bq.qcount[p] = q.qcount; bq.cap[p] = q.cap;
     }
     if (e != cudaSuccess) return e;
-    uint32_t nl = 0;
+    uint32_t nl = 0, compactions = 0, host_syncs = 0;
     if (timed) cudaEventRecord(ws->ev[ev_begin], stream);
     k_wf_begin<<<grid_s, 256, 0, stream>>>(a, w, bq);
     if (timed) cudaEventRecord(ws->ev[ev_begin + 1], stream);
@@ -850,10 +877,13 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
             WfPart& q = ws->part[p];
             if (q.done) continue;
             const int tiles = (int)((q.live + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE);
+            if (timed) cudaEventRecord(ws->ev[ev_begin + 2 + 2 * CRT_WF_MAX_PARTS + 2 * p], q.stream);
             k_compact_count<<<tiles, 256, 0, q.stream>>>(q.queue[q.cur], q.qcount, q.cur, q.tile_count);
             k_compact_scan<<<1, 1024, 0, q.stream>>>(q.tile_count, tiles, q.qcount, q.cur);
             k_compact_scatter<<<tiles, 256, 0, q.stream>>>(q.queue[q.cur], q.queue[q.cur ^ 1], q.qcount, q.cur, q.tile_count);
+            if (timed) cudaEventRecord(ws->ev[ev_begin + 3 + 2 * CRT_WF_MAX_PARTS + 2 * p], q.stream);
             nl += 3;
+            compactions++;
             q.cur ^= 1;
             cudaMemcpyAsync(q.h_qcount, q.qcount, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, q.stream);
         }
@@ -862,15 +892,18 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
             WfPart& q = ws->part[p];
             if (q.done) continue;
             e = cudaStreamSynchronize(q.stream);
+            host_syncs++;
             if (e != cudaSuccess) break;
             q.live = q.h_qcount[q.cur];
             if (q.live == 0u) q.done = true; else active++;
         }
         if (e == cudaSuccess && timed) {
             float ms = 0.f;
-            if (first) { cudaEventElapsedTime(&ms, ws->ev[ev_begin], ws->ev[ev_begin + 1]); times->shade_ms += ms; times->shade_launches++; first = false; }
+            if (first) { cudaEventElapsedTime(&ms, ws->ev[ev_begin], ws->ev[ev_begin + 1]); times->begin_ms += ms; first = false; }
             for (int p = 0; p < parts; p++) {
                 if (!timed_part[p]) continue;
+                cudaEventElapsedTime(&ms, ws->ev[ev_begin + 2 + 2 * CRT_WF_MAX_PARTS + 2 * p], ws->ev[ev_begin + 3 + 2 * CRT_WF_MAX_PARTS + 2 * p]);
+                times->compact_ms += ms;
                 if (tail_part[p]) {
                     cudaEventElapsedTime(&ms, ws->ev[ev_begin + 2 + 2 * p], ws->ev[ev_begin + 3 + 2 * p]); times->tail_ms += ms;
                     continue;
@@ -896,8 +929,15 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         if (active == 0) break;
     }
     // every part's stream was synchronised by the host above, so work queued on `stream` after this call is ordered
-    // behind the side stream's kernels as well
+    // behind the side stream's kernels as well. After an error the side streams may still hold work of the batch
+    // that failed: wait for them too, so that nothing of this frame runs behind the caller's back.
+    if (e != cudaSuccess)
+        for (int p = 0; p < parts; p++) if (ws->part[p].stream) (void)cudaStreamSynchronize(ws->part[p].stream);
+    if (e == cudaSuccess && incomplete) {   // the iteration bound was reached with pixels still live: the frame is NOT finished
+        for (int p = 0; p < parts; p++) if (!ws->part[p].done) *incomplete = true;
+    }
     if (launches) *launches += nl;
+    if (times) { times->host_syncs += host_syncs; times->compactions += compactions; times->iterations += (uint32_t)it; }
     return e;
 }
 

@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol(crt):
     for name in names:
         assert hasattr(lib, name), name
     assert sorted(crt.API_FUNCTIONS) == names
-    assert lib.crt_api_version() == 1
+    assert lib.crt_api_version() == 2
 
 
 def test_struct_sizes_match_header(crt):
@@ -31,7 +31,7 @@ def test_struct_sizes_match_header(crt):
     assert C.sizeof(crt.Camera) == 48
     assert C.sizeof(crt.Config) == 48
     assert C.sizeof(crt.RenderParams) == 32
-    assert C.sizeof(crt.Stats) == 104
+    assert C.sizeof(crt.Stats) == 120
 
 
 def test_no_cpu_fallback(crt, gpu_available):
