@@ -60,6 +60,7 @@ struct WavefrontState {
     cudaEvent_t ev_fork = nullptr;
     size_t n = 0;
     int blocks_extend = 0, blocks_shade = 0;
+    int shade_bulk = 1;              // env CRT_SHADE_BULK: shade's path state arrives through cp.async.bulk (k_wf_shade_bulk); 0 = per-thread loads (k_wf_shade)
     int extend_reverse = 1;          // env CRT_EXTEND_REVERSE: extend consumes the queue back to front (L2 reuse of what shade just wrote)
     int fetch_lanes = CRT_FETCH_LANES, postpone_lanes = CRT_POSTPONE_LANES, coop = 0, shade_persistent = 1;   // tuning knobs (env CRT_FETCH_LANES / CRT_POSTPONE_LANES)
     int drain_rounds = 4;            // env CRT_DRAIN_ROUNDS: rounds a warp keeps going after the queue ran out, then it suspends its rays (0 = never suspend)
@@ -247,7 +248,7 @@ struct WarpPool {
 #define CRT_EXTEND_THREADS 256
 #endif
 #ifndef CRT_SMEM_STACK
-#define CRT_SMEM_STACK 0   // entries of the traversal stack kept in shared memory (0 = all in local memory); see DESIGN.md 3.2
+#define CRT_SMEM_STACK 4   // entries of the traversal stack kept in shared memory (0 = all in local memory); see DESIGN.md 3.2
 #endif
 #ifndef CRT_EXTEND_MIN_BLOCKS
 #define CRT_EXTEND_MIN_BLOCKS (1024 / CRT_EXTEND_THREADS)
@@ -610,6 +611,152 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
     }
 }
 
+// ---- shade, fed by the bulk-copy engine ---------------------------------------------------------------
+// The queue stays in pixel order and (until pixels start to finish, ~85 % of a 2000-spp frame) without holes, so
+// the 32 entries a warp takes per trip are 32 CONSECUTIVE pixels: their A, B, C records are three contiguous
+// 512-byte runs and their six RNG words six contiguous 128-byte runs. One lane hands those nine runs to the
+// bulk asynchronous copy engine (cp.async.bulk global -> shared, completion counted on an mbarrier; the 1-D form
+// of TMA) ONE TRIP AHEAD, into the other of the warp's two 2304-byte stages; the lanes then read their entry
+// from shared memory. The per-thread version above issues 9 dependent loads + 9 L2 prefetches per entry and
+// still starts every trip with an L2 round trip; here the state of the next trip is already on the SM when
+// the trip begins, and the load/prefetch/address instructions are gone. Each warp owns its stages and
+// barriers: no CTA-wide synchronisation, warps drift apart as their rejection loops dictate.
+// A warp whose 32 entries are not one aligned run (holes after pixels finished, the ragged end of the queue)
+// falls back to per-thread loads for that trip (with the L2 prefetch one trip ahead). Results leave through plain
+// coalesced stores. Same arithmetic per pixel: the frame's bits do not change (the parity tests run both kernels).
+#define CRT_SHADE_STAGE_BYTES 2304u   // 3 x 512 (A, B, C) + 6 x 128 (RNG planes)
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0u;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    // a bulk copy that never completes would hang the GPU: trap instead (a few seconds of polling)
+    for (uint32_t spin = 0; !mbar_try_wait(bar, parity); spin++)
+        if (spin > (1u << 26)) __trap();
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+__global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade_bulk(RenderArgs a, WfView w, uint32_t* queue, uint32_t* qcount, int cur, int par) {
+    __shared__ __align__(128) unsigned char stages[8][2][CRT_SHADE_STAGE_BYTES];
+    __shared__ __align__(8) unsigned long long bars[8][2];
+    const uint32_t count = qcount[cur];
+    const uint32_t rounded = (count + 31u) & ~31u;
+    const size_t n = (size_t)a.rc.width * a.rc.height;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t first = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    const bool planes_aligned = (n & 3u) == 0u;   // every RNG plane starts on a 16-byte boundary
+    const uint32_t bar0 = smem_addr(&bars[warp][0]), stage0 = smem_addr(&stages[warp][0][0]);
+    if (lane == 0) {
+        mbar_init(bar0, 1u);
+        mbar_init(bar0 + 8u, 1u);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    uint32_t phase_bits = 0u, bulk_bits = 0u;   // per stage: parity to wait for / the stage was filled by the copy engine (warp-uniform)
+    // the warp's queue words of this trip, the next and the one after (64-bit index: first + 2*stride may pass 2^32)
+    auto queue_word = [&](unsigned long long i) -> uint32_t { return i < (unsigned long long)count ? queue[i] : QUEUE_DEAD; };
+    auto issue = [&](uint32_t st, uint32_t qw) {
+        const uint32_t qbase = __shfl_sync(0xffffffffu, qw, 0);
+        const bool run = __all_sync(0xffffffffu, qw != QUEUE_DEAD && qw == qbase + lane) && planes_aligned && (qbase & 3u) == 0u;
+        if (run) {
+            if (lane == 0) {
+                const uint32_t bar = bar0 + 8u * st, dst = stage0 + CRT_SHADE_STAGE_BYTES * st;
+                mbar_expect_tx(bar, CRT_SHADE_STAGE_BYTES);
+                bulk_g2s(dst, w.A + qbase, 512u, bar);
+                bulk_g2s(dst + 512u, w.B + qbase, 512u, bar);
+                bulk_g2s(dst + 1024u, w.C + qbase, 512u, bar);
+#pragma unroll
+                for (uint32_t k = 0; k < 6u; k++) bulk_g2s(dst + 1536u + 128u * k, a.fb.rng + (size_t)k * n + qbase, 128u, bar);
+            }
+            bulk_bits |= 1u << st;
+        } else {
+            bulk_bits &= ~(1u << st);
+            if (qw != QUEUE_DEAD) {
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(w.A + qw));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(w.B + qw));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(w.C + qw));
+#pragma unroll
+                for (int k = 0; k < 6; k++) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.fb.rng + (size_t)k * n + qw));
+            }
+        }
+        if (qw != QUEUE_DEAD) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.fb.accum + qw));   // read only when a path ends
+    };
+    uint32_t q_cur = queue_word(first), q_next = queue_word((unsigned long long)first + stride);
+    if (first < rounded) issue(0u, q_cur);
+    uint32_t st = 0u;
+    for (uint32_t i = first; i < rounded; st ^= 1u) {
+        const uint32_t pix = q_cur;
+        const unsigned long long i_next = (unsigned long long)i + stride;
+        const uint32_t q_after = queue_word(i_next + stride);
+        // the other stage was read to registers in the last trip (a __syncwarp ago): refill it for the next one
+        if (i_next < (unsigned long long)rounded) issue(st ^ 1u, q_next);
+        float4 A, B, C;
+        Rng rng;
+        A = B = C = make_float4(0.f, 0.f, 0.f, 0.f);
+        rng.v0 = rng.v1 = rng.v2 = rng.v3 = rng.v4 = rng.d = 0u;
+        if ((bulk_bits >> st) & 1u) {
+            mbar_wait(bar0 + 8u * st, (phase_bits >> st) & 1u);
+            phase_bits ^= 1u << st;
+            const unsigned char* sb = &stages[warp][st][0];
+            A = reinterpret_cast<const float4*>(sb)[lane];
+            B = reinterpret_cast<const float4*>(sb + 512)[lane];
+            C = reinterpret_cast<const float4*>(sb + 1024)[lane];
+            const uint32_t* sr = reinterpret_cast<const uint32_t*>(sb + 1536);
+            rng.v0 = sr[lane]; rng.v1 = sr[32 + lane]; rng.v2 = sr[64 + lane];
+            rng.v3 = sr[96 + lane]; rng.v4 = sr[128 + lane]; rng.d = sr[160 + lane];
+        } else if (pix != QUEUE_DEAD) {
+            A = w.A[pix]; B = w.B[pix]; C = w.C[pix];
+            rng = wf_load_rng(a.fb.rng, n, pix);
+        }
+        __syncwarp();
+        if (pix != QUEUE_DEAD && C.x != PARKED_T) {   // a parked pixel waits for extend to finish its ray: nothing is touched
+            vec3 o = mk3(A.x, A.y, A.z), d = mk3(B.x, B.y, B.z), thr = mk3(fabsf(A.w), B.w, C.z);   // |A.w|: PARKED_SIGN may be left on it
+            const uint32_t book = __float_as_uint(C.w);
+            int sample = (int)(book & 0xffffffu), bounce = (int)(book >> 24);
+            bool touched = false;
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            const bool keep = shade_step(a, pix, o, d, thr, sample, bounce, rng, C.x, __float_as_uint(C.y), acc, touched);
+            if (touched) {
+                if (!keep) {
+                    acc.w += (float)a.rc.spp;
+                    if (!(a.flags & CRT_RENDER_NO_TONEMAP))
+                        a.fb.rgba8[pix] = pack_rgba8(v_scale(mk3(acc.x, acc.y, acc.z), f_div(1.f, acc.w)));
+                }
+                a.fb.accum[pix] = acc;
+            }
+            wf_store_rng(a.fb.rng, n, pix, rng);
+            if (keep) {
+                w.A[pix] = make_float4(o.x, o.y, o.z, thr.x);
+                w.B[pix] = make_float4(d.x, d.y, d.z, thr.y);
+                float2* c2 = reinterpret_cast<float2*>(&w.C[pix]) + 1;
+                *c2 = make_float2(thr.z, __uint_as_float((uint32_t)sample | ((uint32_t)bounce << 24)));
+            } else {
+                queue[i] = QUEUE_DEAD;   // all samples of this pixel are done
+            }
+        }
+        q_cur = q_next;
+        q_next = q_after;
+        if (i_next >= (unsigned long long)rounded) break;
+        i = (uint32_t)i_next;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        qcount[2] = 0u;                // fetch cursor of the next extend
+        qcount[4 + (par ^ 1)] = 0u;    // the parked-ray list the extend before this shade has consumed: the next extend fills it
+    }
+}
+
 // ---- tail: the last pixels of a frame, a thread per pixel for many iterations at a time ------------------
 // A pixel's samples are sequential (its cuRAND stream), so the frame ends with a few pixels (those with the
 // longest paths) that still owe hundreds of iterations. With a short queue an iteration costs what its longest
@@ -728,7 +875,9 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
     if (e == cudaSuccess && s->parts > 1) e = cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming);
     int be = 0, bs = 0;
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&be, k_wf_extend<false, false>, CRT_EXTEND_THREADS, 0);
-    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade, 256, 0);
+    if (const char* v = getenv("CRT_SHADE_BULK")) s->shade_bulk = atoi(v);
+    if (e == cudaSuccess) e = s->shade_bulk ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade_bulk, 256, 0)
+                                            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade, 256, 0);
     if (const char* v = getenv("CRT_FETCH_LANES")) s->fetch_lanes = atoi(v);
     if (const char* v = getenv("CRT_EXTEND_REVERSE")) s->extend_reverse = atoi(v);
     if (const char* v = getenv("CRT_COOP")) s->coop = atoi(v);
@@ -866,7 +1015,8 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                 else if (ws->coop) k_wf_extend<false, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
                 else k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
                 if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p) + 1], st);
-                k_wf_shade<<<shade_grid, 256, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur, par);
+                if (ws->shade_bulk) k_wf_shade_bulk<<<shade_grid, 256, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur, par);
+                else k_wf_shade<<<shade_grid, 256, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur, par);
                 if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p) + 2], st);
                 nl += 2;
             }

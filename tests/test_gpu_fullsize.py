@@ -103,7 +103,7 @@ def test_c3_spheres_full_size_radiance(crt, mode):
     crops = [(540, 360, 128, 64), (0, 0, 96, 48), (1104, 752, 96, 48), (300, 420, 96, 64), (800, 300, 96, 64)]
     st, seen = _check_crops(crt, sc, osc, 1200, 800, 4, 20, crops, crt.MODE_MEGAKERNEL if mode == "mega" else crt.MODE_WAVEFRONT,
                             min_exact=0.998)
-    assert len(seen) > 20 and -1 in seen                    # many spheres and the sky
+    assert len(seen) > 8 and -1 in seen                     # several spheres and the sky
     osc.close()
     sc.free()
 

@@ -75,19 +75,27 @@ def test_matched_seed_radiance(crt, mode, name, param, W, H, spp, bounces):
     sc.free()
 
 
-def test_wavefront_equals_megakernel_bitwise(crt):
+@pytest.mark.parametrize("W,H,spp", [(200, 120, 6), (256, 160, 24), (203, 117, 5)])
+def test_wavefront_equals_megakernel_bitwise(crt, W, H, spp, monkeypatch):
+    """Megakernel, wavefront with the bulk-copy-fed shade kernel (k_wf_shade_bulk: aligned 32-pixel runs through
+    cp.async.bulk + mbarrier, everything else through its per-thread fallback) and wavefront with the per-thread shade
+    kernel (CRT_SHADE_BULK=0) give the same bits. 203x117: W*H is not a multiple of 4, so the RNG planes are not
+    16-byte aligned and every warp takes the fallback; 24 spp: pixels finish at different iterations, the queue gets
+    holes and is compacted while other warps still run on aligned runs."""
     sc = crt.builtin_scene("cornell_blob", 48)
-    W, H = 200, 120
     out = []
-    for mode in (crt.MODE_MEGAKERNEL, crt.MODE_WAVEFRONT):
-        r = make_renderer(crt, sc, W, H, mode)
-        st = r.render(6, 20)
+    for mode, bulk in ((crt.MODE_MEGAKERNEL, None), (crt.MODE_WAVEFRONT, "1"), (crt.MODE_WAVEFRONT, "0")):
+        if bulk is not None:
+            monkeypatch.setenv("CRT_SHADE_BULK", bulk)
+        r = make_renderer(crt, sc, W, H, mode, aspect=W / H)
+        st = r.render(spp, 20)
         out.append((r.accum().copy(), r.image_rgba8().copy(), r.rng_state().copy(), int(st.rays)))
         r.close()
-    assert np.array_equal(out[0][0].view(np.uint32), out[1][0].view(np.uint32))
-    assert np.array_equal(out[0][1], out[1][1])
-    assert np.array_equal(out[0][2], out[1][2])
-    assert out[0][3] == out[1][3]
+    for k in (1, 2):
+        assert np.array_equal(out[0][0].view(np.uint32), out[k][0].view(np.uint32))
+        assert np.array_equal(out[0][1], out[k][1])
+        assert np.array_equal(out[0][2], out[k][2])
+        assert out[0][3] == out[k][3]
     sc.free()
 
 
