@@ -135,7 +135,7 @@ def run_reference(args):
         print(json.dumps(dict(base, unavailable="oracle/_ref/ref_render_b20 not built (needs /root/reference at build time)")))
         return 0
     cmd = [exe, "--scene", args.scene, "--param", str(args.param), "--width", str(args.width), "--height", str(args.height),
-           "--spp", str(args.ref_spp), "--frames", str(args.steps), "--warmup", str(args.warmup), "--seed", str(SEED), "--twin"]
+           "--spp", str(args.ref_spp), "--frames", str(args.steps), "--warmup", str(args.warmup), "--seed", str(SEED), "--twin", "--rewind"]
     clk = ClockSampler(0)
     clk.start()
     t0 = time.perf_counter()
@@ -155,6 +155,9 @@ def run_reference(args):
                         "scene_triangles": r["triangles"], "stack_bytes": r["stack_bytes"]},
                 frame_ms_2000spp_extrapolated=r["frame_ms_mean"] * args.spp / args.ref_spp,
                 rays_per_step=r["rays_frame0"], twin_matches_render=r["twin_matches_render"],
+                rays_counted_on="every timed frame: the RNG streams are rewound (untimed) before each frame, so each one is frame 0 bit for bit, "
+                                "whose rays the untimed twin kernel counted" if r.get("rewind") else "frame 0 only",
+                same_config=(args.ref_spp == args.spp),
                 cpu_baseline={"value": mrays, "unit": "Mrays/s", "cores": 0, "kind": "reference",
                               "sample": "reference CUDA kernel on the GPU (upstream has no CPU renderer), %d spp" % args.ref_spp},
                 e2e={"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -162,6 +165,65 @@ def run_reference(args):
                 clocks=clocks, wall_s=wall, gpu_launches=args.steps)
     print(json.dumps(line))
     return 0
+
+
+def crc32_of(arr):
+    import zlib
+    return zlib.crc32(np.ascontiguousarray(arr).tobytes()) & 0xffffffff
+
+
+def kernel_rooflines(args, kst, st_counted, build, peaks, l2_gbs, traffic_json, world, W, H):
+    """Per-kernel roofline rows (DESIGN.md section 6 states each bytes model). kst = crt_stats of the per-kernel timing pass."""
+    hbm = peaks["hbm_gbs"]
+    npx = W * H
+    rays, samples = float(kst.rays), float(kst.samples)
+    cache_resident = args.scene != "terrain"
+    n_bar, t_bar = st_counted.nodes_fetched / st_counted.rays, st_counted.prims_tested / st_counted.rays
+    b_ray = 80.0 * n_bar + 48.0 * t_bar + 44.0
+    rows = []
+
+    def row(name, bound, peak, nbytes, ms, launches, model, extra=None):
+        ach = nbytes / (ms * 1e-3) / 1e9 if ms and ms > 0 else None
+        r = {"kernel": name, "bound": bound, "bytes_model": model, "algorithmic_bytes": nbytes, "ms": ms, "launches": launches,
+             "achieved_gbs": ach, "peak_gbs": peak, "frac": (ach / peak) if (ach and peak) else None}
+        tj = traffic_json.get(name)
+        if tj and launches:
+            # DRAM bytes of ONE launch from the committed ncu --set full capture, scaled by this run's average launch time
+            r["ncu_dram_bytes_per_launch"] = tj.get("dram_bytes_per_launch")
+            r["ncu_dram_gbs"] = tj.get("dram_bytes_per_launch") / (tj.get("gpu_time_us") * 1e-6) / 1e9 if tj.get("gpu_time_us") else None
+            r["ncu_dram_frac_of_hbm"] = (r["ncu_dram_gbs"] / hbm) if r.get("ncu_dram_gbs") else None
+            r["ncu_source"] = tj.get("source")
+        if extra:
+            r.update(extra)
+        rows.append(r)
+        return r
+
+    ext = row("k_wf_extend", "l2" if cache_resident else "hbm", l2_gbs if cache_resident else hbm, b_ray * rays, kst.extend_ms, int(kst.extend_launches),
+              "80 B x nodes/ray + 48 B x records/ray + 44 B (32 B ray read, 8 B hit write, 4 B queue word), counted by crt_render_counted",
+              {"bytes_per_ray": b_ray, "nodes_per_ray": n_bar, "prims_per_ray": t_bar,
+               "limiter": "SIMT divergence + dependent-load latency (profiles/: lanes per instruction, long-scoreboard); the scene is served from L1/L2"
+                          if cache_resident else "dependent-load latency on a 306 MB scene (DRAM counters in ncu_dram_*)"})
+    row("k_wf_shade", "hbm", hbm, rays * 140.0 + samples * 32.0, kst.shade_ms, int(kst.shade_launches),
+        "per queue entry 48 B state + 24 B RNG read, 40 B state + 24 B RNG written, 4 B queue word; per finished path 16 B accumulator read + 16 B written")
+    row("k_wf_begin", "hbm", hbm, npx * 116.0, kst.begin_ms, 1,
+        "per pixel 24 B RNG read + 24 B written, 48 B state, 16 B accumulator, 4 B queue word written")
+    row("k_compact_count+scan+scatter", "hbm (launch-latency at this size)", hbm, None, kst.compact_ms, None,
+        "12 B per queue entry per compaction (count reads 4 B, scatter reads 4 B and writes <= 4 B); three launches of a few microseconds each, "
+        "every 16 iterations", {"algorithmic_bytes": None})
+    row("k_wf_tail", "latency (the frame's serial tail: few pixels, each a chain of dependent path segments)", None, None, kst.tail_ms, None,
+        "no byte model: the last <= 150 k pixels per part, one thread per pixel")
+    row("k_rng_init", "alu (cuRAND skip-ahead: 2^67 x subsequence jump per pixel, matrix products in registers)", hbm, npx * 24.0, build.rng_init_ms, 1,
+        "24 B written per pixel; outside the frame (once per crt_init_rng)")
+    row("bvh build (k_for_n<...> + cub sort/scan)", "launch latency (one short launch per PLOC step)", None, None, build.bvh_build_ms, None,
+        "outside the frame (once per crt_set_scene); %d wide nodes" % int(build.bvh_nodes))
+    if world > 1:
+        rows.append({"kernel": "ncclReduce + k_tonemap", "bound": "nvlink / hbm", "bytes_model": "16 B per pixel per rank over NVLink, then 16 B read + 4 B written per pixel on the root",
+                     "algorithmic_bytes": npx * 16.0 * (world - 1) + npx * 20.0})
+    tot_ms = kst.extend_ms + kst.shade_ms + kst.begin_ms + kst.compact_ms + kst.tail_ms
+    for r in rows:
+        if r.get("ms") is not None and r["kernel"] in ("k_wf_extend", "k_wf_shade", "k_wf_begin", "k_compact_count+scan+scatter", "k_wf_tail"):
+            r["share_of_frame_kernel_time"] = r["ms"] / tot_ms if tot_ms > 0 else None
+    return ext, rows
 
 
 def main():
@@ -183,6 +245,10 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: libcrt_b200 has no CPU fallback")
     torch.cuda.set_device(local)
+    # a stream of our own: the library launches on it, torch's events are recorded on it, and the library's NCCL reduce
+    # runs on it too (handle 0, the legacy default stream, cannot be handed to crt_set_stream)
+    stream = torch.cuda.Stream(device=local)
+    torch.cuda.set_stream(stream)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -198,11 +264,16 @@ def main():
     build = r.stats()
     my_spp = mg.shard_spp(args.spp, world, rank)
     flags = crt.RENDER_NO_TONEMAP if world > 1 else 0
-    # the library launches on torch's current stream from here on, so torch events and the NCCL reduce
-    # order with the render kernels (torch.cuda.Event only sees torch's current stream)
-    stream = torch.cuda.current_stream()
     r.set_stream(stream.cuda_stream)
-    acc_t = mg.accum_as_tensor(torch, r.accum_device_ptr(), H, W, local) if world > 1 else None
+    if world > 1:
+        # the library's own communicator (crt_comm_init = ncclCommInitRank): rank 0's id travels over torch.distributed,
+        # which is plumbing here (rendezvous, barrier, the max over ranks of the timings); the frame's ONE collective,
+        # the sum-reduce of the float4 buffer, is crt_reduce_accum inside the library, on the render's stream
+        idt = torch.zeros(crt.COMM_ID_BYTES, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(crt.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, src=0)
+        r.comm_init(bytes(idt.cpu().numpy().tobytes()), world, rank)
     host_img = np.empty((H, W, 4), np.uint8)
 
     def sync_all():
@@ -211,14 +282,12 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    def step(time_kernels=False, e2e=False):
+    def step(time_kernels=False, e2e=False, spp=None):
         if e2e:
             r.update_camera(cam)              # per-frame host->device input, like CUDARenderer::updateCamera
-        st = r.render(my_spp, args.bounces, flags=flags | (crt.RENDER_TIME_KERNELS if time_kernels else 0))
-        if dist is not None:
-            mg.reduce_accum(acc_t, dist, dst=0)
-            if rank == 0:
-                r.tonemap()
+        st = r.render(my_spp if spp is None else spp, args.bounces, flags=flags | (crt.RENDER_TIME_KERNELS if time_kernels else 0))
+        if world > 1:
+            r.reduce_accum(0)                 # ncclReduce(sum) onto rank 0 + tonemap there, inside the library
         if e2e and rank == 0:
             r.image_rgba8(host_img)           # device->host frame, like WindowManager::drawFrame
         return st
@@ -226,16 +295,16 @@ def main():
     def timed(n, **kw):
         """n steps bracketed by barrier + synchronize, timed with CUDA events on the launching stream."""
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        acc = {"rays": 0, "launches": 0, "ext_ms": 0.0, "shade_ms": 0.0, "ext_launches": 0}
+        acc = {"rays": 0, "launches": 0, "host_syncs": 0, "iterations": 0, "last": None}
         sync_all()
         ev0.record(stream)
         for _ in range(n):
             st = step(**kw)
             acc["rays"] += int(st.rays)
             acc["launches"] += int(st.kernel_launches) + (1 if world > 1 and rank == 0 else 0)
-            acc["ext_ms"] += st.extend_ms
-            acc["shade_ms"] += st.shade_ms
-            acc["ext_launches"] += int(st.extend_launches)
+            acc["host_syncs"] += int(st.host_syncs)
+            acc["iterations"] += int(st.iterations)
+            acc["last"] = st
         ev1.record(stream)
         sync_all()
         acc["ms"] = ev0.elapsed_time(ev1)
@@ -248,70 +317,111 @@ def main():
         clk.start()
     main_run = timed(args.steps)
     clocks = clk.finish() if rank == 0 else None
+    # check: the frame the timed region just produced (rank 0 holds the reduced buffer)
+    check = None
+    if rank == 0:
+        accw = r.accum()[..., 3]
+        check = {"accum_w_min": float(accw.min()), "accum_w_max": float(accw.max()), "expected_w": float(args.spp),
+                 "rgba8_crc32": crc32_of(r.image_rgba8()), "frame": "last frame of the timed region, rank 0 after the reduce"}
     # per-kernel-class times (events between the launches perturb the pipeline a little: separate, untimed-for-value pass)
     k_run = timed(1, time_kernels=True)
     # e2e: the same frames through the public API with host buffers inside the timed region
     e_run = timed(args.steps, e2e=True)
 
-    tot = torch.tensor([float(main_run["rays"]), float(e_run["rays"]), float(main_run["launches"])], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([float(main_run["rays"]), float(e_run["rays"]), float(main_run["launches"]), float(main_run["host_syncs"])],
+                       dtype=torch.float64, device="cuda")
     mx = torch.tensor([main_run["ms"], e_run["ms"]], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-    rays_all, e_rays_all, launches_all = tot[0].item(), tot[1].item(), tot[2].item()
+    rays_all, e_rays_all, launches_all, syncs_all = tot[0].item(), tot[1].item(), tot[2].item(), tot[3].item()
     dt, dt_e2e = mx[0].item() * 1e-3, mx[1].item() * 1e-3
+
+    # N > 1: does every rank's shard land in rank 0's buffer, and is a shard what a single GPU renders from that base?
+    if world > 1:
+        vs = 4                                            # samples per rank of the verification frame
+        x0, y0, cw, ch = W // 2 - 64, H // 2 - 32, 128, 64
+        r.initialize(SEED, mg.subsequence_base(rank, W, H))
+        r.render(vs, args.bounces, flags=crt.RENDER_NO_TONEMAP)
+        mine = torch.from_numpy(r.accum()[y0:y0 + ch, x0:x0 + cw].copy()).cuda()
+        shards = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(shards, mine)
+        r.reduce_accum(0)
+        if rank == 0:
+            red = r.accum()
+            want = np.zeros((ch, cw, 4), np.float32)
+            for t in shards:
+                want += t.cpu().numpy()
+            got = red[y0:y0 + ch, x0:x0 + cw]
+            g = world - 1
+            r.initialize(SEED, mg.subsequence_base(g, W, H))
+            r.render(vs, args.bounces, flags=crt.RENDER_NO_TONEMAP)
+            solo = r.accum()[y0:y0 + ch, x0:x0 + cw]
+            check["multi_gpu"] = {
+                "verification_frame": "%d spp per rank, crop %dx%d at (%d,%d)" % (vs, cw, ch, x0, y0),
+                "reduced_w_min": float(red[..., 3].min()), "reduced_w_max": float(red[..., 3].max()), "expected_w": float(vs * world),
+                "reduced_crop_equals_sum_of_shards": bool(np.allclose(got, want, rtol=1e-6, atol=0.0)),
+                "reduced_crop_max_rel_err": float((np.abs(got - want) / np.maximum(np.abs(want), 1e-6)).max()),
+                "shard_checked": g, "shard_equals_single_gpu_render_from_its_base_bitwise": bool(np.array_equal(solo.view(np.uint32), shards[g].cpu().numpy().view(np.uint32))),
+                "comm": dict(zip(("nranks", "rank", "nccl_version"), r.comm_info()))}
+        dist.barrier()
 
     if rank == 0:
         # algorithmic bytes per ray of the dominant kernel: counted by an instrumented (untimed) bounded render
         r.initialize(SEED, 0)
         c = r.render(2, args.bounces, flags=flags, counted=True)
-        n_bar, t_bar = c.nodes_fetched / c.rays, c.prims_tested / c.rays
-        rec_bytes = 44 if args.mode == "wavefront" else 0      # ray record 32 B + hit record 8 B + queue index 4 B
-        b_ray = 80.0 * n_bar + 48.0 * t_bar + rec_bytes
         peaks, how = measured_peaks()
-        kernel = "k_wf_extend" if args.mode == "wavefront" else "k_render_mega"
-        ext_ms, ext_launches = k_run["ext_ms"], max(k_run["ext_launches"], 1)
-        achieved = (b_ray * k_run["rays"]) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else None
-        traffic, traffic_src = None, None
-        tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
-            try:
-                tj = json.load(open(tp))
-                traffic, traffic_src = tj.get(kernel, {}).get("dram_bytes_per_launch"), tj.get(kernel, {}).get("source")
-            except Exception:
-                pass
         l2 = None   # L2-resident streaming-read bandwidth measured on this pool's B200 by scripts/l2_bw.cu
         try:
             l2j = json.load(open(os.path.join(ROOT, "profiles", "l2_peak.json")))
             l2 = [pt["gbs"] for pt in l2j["points"] if pt["working_set_mb"] == 4][0]
         except Exception:
             pass
-        roof = {"bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": (achieved / peaks["hbm_gbs"]) if achieved else None, "traffic": traffic, "traffic_source": traffic_src,
-                "peak_source": how + " (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)",
-                "bytes_per_ray": b_ray, "nodes_per_ray": n_bar, "prims_per_ray": t_bar,
-                "algorithmic_bytes_per_launch": b_ray * k_run["rays"] / ext_launches,
-                "kernel_ms_per_launch": ext_ms / ext_launches, "kernel_launches_per_step": k_run["ext_launches"],
-                "kernel_share_of_step": ext_ms / k_run["ms"], "shade_ms_per_step": k_run["shade_ms"],
-                "l2_peak_gbs": l2, "frac_of_l2_peak": (achieved / l2) if (achieved and l2) else None,
-                "l2_peak_source": "profiles/l2_peak.json (scripts/l2_bw.cu, 4 MB working set, ld.global.cg)",
-                "note": "extend is bound by divergence and dependent-load latency; where the scene fits the caches (all configs but the "
-                        "5 M-triangle terrain) nodes and triangles are served from L1/L2, so achieved/peak compares cache-served "
-                        "algorithmic bytes with the HBM copy peak; traffic is the ncu capture of the headline scene; see DESIGN.md §3/§6"}
+        traffic_json = {}
+        try:
+            traffic_json = json.load(open(os.path.join(ROOT, "profiles", "traffic_terrain.json" if args.scene == "terrain" else "traffic.json")))
+        except Exception:
+            pass
+        kst = k_run["last"]
+        if args.mode == "wavefront":
+            ext, rows = kernel_rooflines(args, kst, c, build, peaks, l2, traffic_json, world, W, H)
+            cache_resident = args.scene != "terrain"
+            roof = {"bound": "l2" if cache_resident else "hbm", "kernel": "k_wf_extend", "achieved": ext["achieved_gbs"],
+                    "peak": ext["peak_gbs"], "unit": "GB/s", "frac": ext["frac"],
+                    "traffic": ext.get("ncu_dram_bytes_per_launch"), "traffic_source": ext.get("ncu_source"),
+                    "peak_source": ("profiles/l2_peak.json (scripts/l2_bw.cu: 4 MB working set streamed past L1 by all SMs, measured on this pool's B200); "
+                                    "the scene (<= 4.3 MB of nodes + records) is cache resident, SURVEY.md 8(d) names L2 as the bound" if cache_resident
+                                    else how + " (MEASURED_PEAKS.json hbm_gbs, copy bandwidth): the 306 MB scene does not fit the 126 MB L2"),
+                    "bytes_per_ray": ext["bytes_per_ray"], "nodes_per_ray": ext["nodes_per_ray"], "prims_per_ray": ext["prims_per_ray"],
+                    "algorithmic_bytes_per_launch": ext["algorithmic_bytes"] / max(ext["launches"], 1),
+                    "kernel_ms_per_launch": ext["ms"] / max(ext["launches"], 1), "kernel_launches_per_step": ext["launches"],
+                    "kernel_share_of_step": ext["ms"] / k_run["ms"], "hbm_peak_gbs": peaks["hbm_gbs"], "l2_peak_gbs": l2,
+                    "frac_of_hbm_copy_peak": ext["achieved_gbs"] / peaks["hbm_gbs"] if ext["achieved_gbs"] else None,
+                    "achieved_dram_gbs_ncu": ext.get("ncu_dram_gbs"), "achieved_dram_frac_of_hbm_ncu": ext.get("ncu_dram_frac_of_hbm"),
+                    "kernels": rows,
+                    "note": "achieved = algorithmic bytes of k_wf_extend / its summed launch time (CUDA events around every launch, separate pass); "
+                            "kernels[] carries the same for every kernel of the frame; see DESIGN.md section 6"}
+        else:
+            b_ray = 80.0 * c.nodes_fetched / c.rays + 48.0 * c.prims_tested / c.rays
+            ach = b_ray * k_run["rays"] / (kst.extend_ms * 1e-3) / 1e9 if kst.extend_ms > 0 else None
+            roof = {"bound": "l2", "kernel": "k_render_mega", "achieved": ach, "peak": l2, "unit": "GB/s", "frac": (ach / l2) if (ach and l2) else None,
+                    "traffic": None, "bytes_per_ray": b_ray}
         cpu = None if args.no_cpu_baseline or world > 1 else cpu_baseline(crt, args)
         value = rays_all / dt / 1e6
         line = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
                 "config": {"workload": "%s %dx%d %d spp %d bounces (%s); one step = one frame; spp sharded over "
-                                       "ranks, one NCCL reduce of the float4 buffer per frame; per-step state %d MB > L2 (126 MB), so no L2 "
-                                       "flush between steps" % (args.scene, W, H, args.spp, args.bounces, which_config(args), (24 + 16 + 48 + 8) * W * H // 2 ** 20),
+                                       "ranks, one NCCL reduce of the float4 buffer per frame (crt_reduce_accum, inside the library); per-step state %d MB > L2 "
+                                       "(126 MB), so no L2 flush between steps" % (args.scene, W, H, args.spp, args.bounces, which_config(args), (24 + 16 + 48 + 8) * W * H // 2 ** 20),
                            "mode": args.mode, "triangles": sc.num_triangles, "spheres": sc.num_spheres, "seed": SEED,
                            "bvh_nodes": int(build.bvh_nodes), "bvh_build_ms": build.bvh_build_ms, "rng_init_ms": build.rng_init_ms},
                 "frame_ms": dt / args.steps * 1e3, "rays_per_step": rays_all / args.steps,
                 "e2e": {"value": e_rays_all / dt_e2e / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(crt.Camera),
                         "d2h_bytes_per_step": W * H * 4, "ms_per_step": dt_e2e / args.steps * 1e3},
-                "gpu_launches": int(launches_all), "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
+                "gpu_launches": int(launches_all), "launches_per_frame": launches_all / args.steps / world,
+                "host_syncs_per_frame": syncs_all / args.steps / world, "iterations_per_frame": main_run["iterations"] / args.steps,
+                "check": check, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())
     r.close()

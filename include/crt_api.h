@@ -266,6 +266,48 @@ int crt_get_stream(crt_ctx* ctx, void** out_stream);
  * the caller created. */
 int crt_set_stream(crt_ctx* ctx, void* stream);
 
+/* ---- multi-GPU -------------------------------------------------------------
+ * The reference is single-GPU (one device, default stream: src/CUDARenderer.cuh:55-60). Its sample loop
+ * (src/CUDAKernels.h:158-162) shards: GPU g of G renders its share of the samples of EVERY pixel from the
+ * cuRAND subsequences g*width*height + pixel (crt_init_rng's base), then ONE sum-reduce of the float4
+ * accumulation buffers onto a root, which tonemaps. NCCL is bound at run time (libnccl.so.2).
+ *
+ * (a) one process per GPU (torchrun, mpirun): rank 0 calls crt_comm_unique_id and hands the 128 bytes to
+ *     the other ranks; every rank calls crt_comm_init (collective), then per frame
+ *     crt_render(spp_g, CRT_RENDER_NO_TONEMAP) and crt_reduce_accum(root) (collective). */
+#define CRT_COMM_ID_BYTES 128
+int crt_comm_unique_id(void* out_id, size_t bytes);                 /* ncclGetUniqueId */
+int crt_comm_init(crt_ctx* ctx, const void* id, int32_t nranks, int32_t rank);   /* ncclCommInitRank on ctx's device */
+int crt_comm_destroy(crt_ctx* ctx);
+int crt_comm_info(crt_ctx* ctx, int32_t* nranks, int32_t* rank, int32_t* nccl_version);
+/* ncclReduce(sum) of the accumulation buffer, in place, on the context's stream (ordered behind the
+ * render), onto rank `root`; the root then runs crt_tonemap. Returns after the stream has drained: the
+ * buffer may be overwritten by the next frame. Without a communicator it is crt_tonemap. */
+int crt_reduce_accum(crt_ctx* ctx, int32_t root);
+
+/* (b) one process, several GPUs: one context per device inside the library, one host thread per device
+ *     while rendering. Device devices[0] is the root: after crt_group_render its context
+ *     (crt_group_ctx(g, 0)) holds the summed accumulation buffer and the RGBA8 image; read them with the
+ *     crt_get_* calls. With peer access the reduce is ONE kernel on the root that reads every shard over
+ *     NVLink, adds them in device order and tonemaps in the same pass; otherwise (or with
+ *     CRT_GROUP_FORCE_NCCL) ncclReduce + crt_tonemap. */
+#define CRT_GROUP_MAX_DEVICES 16
+enum { CRT_GROUP_FORCE_NCCL = 1u << 0 };
+typedef struct crt_group crt_group;
+int  crt_group_create(crt_group** out, const crt_config* cfg /* .device ignored */, const int32_t* devices, int32_t num_devices);
+void crt_group_destroy(crt_group* g);
+const char* crt_group_last_error(const crt_group* g);
+int32_t crt_group_size(const crt_group* g);
+crt_ctx* crt_group_ctx(crt_group* g, int32_t index);               /* borrowed */
+int crt_group_set_scene(crt_group* g, const crt_scene* scene);       /* uploads + builds the BVH on every device */
+int crt_group_set_camera(crt_group* g, const crt_camera* cam);
+int crt_group_init_rng(crt_group* g, uint64_t seed);                 /* device i: subsequence base i*width*height */
+/* params->spp is the frame's TOTAL sample count: device i renders spp/G (+1 for i < spp%G). */
+int crt_group_render(crt_group* g, const crt_render_params* params, uint32_t group_flags);
+/* sum of the per-device ray / sample / launch counters (render_ms = slowest device), the device time of the
+ * last reduce step, and whether the peer-memory kernel is in use. Any pointer may be NULL. */
+int crt_group_get_stats(crt_group* g, crt_stats* out_sum, float* out_reduce_ms, int32_t* out_peer);
+
 /* ---- built-in procedural scenes (BASELINE.json configs; assets/ is absent upstream) ---
  * names: "cornell" (C1), "cornell_blob" (C2/C5), "spheres" (C3), "terrain" (C4).
  * param: scene-specific size knob (0 = default; blob/terrain: grid resolution scale).

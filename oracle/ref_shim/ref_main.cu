@@ -203,6 +203,7 @@ struct Args {
     unsigned long long seed = 1804289383ull;   // glibc rand() first value (CUDARenderer.cuh:46)
     std::string dump;                            // prefix for binary dumps ("" = none)
     bool twin = false;                           // run the counting twin (untimed)
+    bool rewind = false;                         // re-run initRandState (untimed) before every timed frame: each frame is then frame 0, whose rays the twin counted
     bool primary = false;                        // dump primary ids
     bool rngkat = false;
     int stack = 8192;
@@ -342,6 +343,7 @@ static bool parse_args(int argc, char** argv, Args& a) {
         else if (k == "--seed") a.seed = strtoull(need("--seed"), nullptr, 10);
         else if (k == "--dump") a.dump = need("--dump");
         else if (k == "--twin") a.twin = true;
+        else if (k == "--rewind") a.rewind = true;
         else if (k == "--primary") a.primary = true;
         else if (k == "--rngkat") a.rngkat = true;
         else if (k == "--stack") a.stack = atoi(need("--stack"));
@@ -478,6 +480,7 @@ int main(int argc, char** argv) {
         // ---- timed frames: the reference's own CUDARenderer::render -----------------------
         std::vector<float> frame_ms;
         for (int f = 0; f < a.warmup + a.frames; f++) {
+            if (a.rewind && f > 0) init_rng();   // untimed: the timed frame below then traces exactly rays_frame0 rays
             CK(cudaEventRecord(e0));
             renderer.render(world.dNodes, world.dWorld);
             CK(cudaEventRecord(e1));
@@ -534,11 +537,11 @@ int main(int argc, char** argv) {
         double mean = frame_ms.empty() ? 0.0 : sum / frame_ms.size();
         printf("{\"impl\": \"reference\", \"scene\": \"%s\", \"param\": %d, \"width\": %d, \"height\": %d, \"spp\": %d, "
                "\"max_bounces\": %d, \"seed\": %llu, \"frames\": %d, \"warmup\": %d, \"frame_ms_mean\": %.4f, "
-               "\"frame_ms_min\": %.4f, \"frame_ms_max\": %.4f, \"rays_frame0\": %llu, \"twin_matches_render\": %d, "
+               "\"frame_ms_min\": %.4f, \"frame_ms_max\": %.4f, \"rays_frame0\": %llu, \"rewind\": %d, \"twin_matches_render\": %d, "
                "\"rng_init_ms\": %.3f, \"mesh_bvh_build_ms\": %.3f, \"world_ms\": %.3f, \"top_bvh_ms\": %.3f, "
                "\"triangles\": %u, \"spheres\": %u, \"objects\": %d, \"gpu\": \"%s\", \"stack_bytes\": %d}\n",
                a.scene.c_str(), a.param, W, H, a.spp, (int)REF_MAX_BOUNCES, a.seed, a.frames, a.warmup, mean,
-               frame_ms.empty() ? 0.0 : mn, mx, rays, twin_matches, rng_ms, world.mesh_build_ms, world.world_ms,
+               frame_ms.empty() ? 0.0 : mn, mx, rays, a.rewind ? 1 : 0, twin_matches, rng_ms, world.mesh_build_ms, world.world_ms,
                world.top_bvh_ms, scene.num_triangles(), scene.num_spheres(), world.numObjects, prop.name, a.stack);
         fflush(stdout);
         return 0;

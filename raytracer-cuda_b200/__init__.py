@@ -114,6 +114,21 @@ def load_library():
         "crt_write_pfm": (C.c_int, [P, C.c_char_p]),
         "crt_checkpoint_save": (C.c_int, [P, C.c_char_p]),
         "crt_checkpoint_load": (C.c_int, [P, C.c_char_p]),
+        "crt_comm_unique_id": (C.c_int, [P, C.c_size_t]),
+        "crt_comm_init": (C.c_int, [P, P, C.c_int32, C.c_int32]),
+        "crt_comm_destroy": (C.c_int, [P]),
+        "crt_comm_info": (C.c_int, [P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+        "crt_reduce_accum": (C.c_int, [P, C.c_int32]),
+        "crt_group_create": (C.c_int, [C.POINTER(P), C.POINTER(Config), C.POINTER(C.c_int32), C.c_int32]),
+        "crt_group_destroy": (None, [P]),
+        "crt_group_last_error": (C.c_char_p, [P]),
+        "crt_group_size": (C.c_int32, [P]),
+        "crt_group_ctx": (P, [P, C.c_int32]),
+        "crt_group_set_scene": (C.c_int, [P, C.POINTER(Scene)]),
+        "crt_group_set_camera": (C.c_int, [P, C.POINTER(Camera)]),
+        "crt_group_init_rng": (C.c_int, [P, C.c_uint64]),
+        "crt_group_render": (C.c_int, [P, C.POINTER(RenderParams), C.c_uint32]),
+        "crt_group_get_stats": (C.c_int, [P, C.POINTER(Stats), C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)   # AttributeError here = the header and the library disagree
@@ -127,7 +142,12 @@ API_FUNCTIONS = ["crt_api_version", "crt_create", "crt_destroy", "crt_last_error
                  "crt_set_camera", "crt_render", "crt_render_counted", "crt_primary_ids", "crt_get_image_rgba8",
                  "crt_get_accum", "crt_set_accum", "crt_tonemap", "crt_get_rng_state", "crt_set_rng_state",
                  "crt_get_stats", "crt_get_stream", "crt_set_stream", "crt_scene_builtin", "crt_scene_free", "crt_scene_load_obj",
-                 "crt_write_ppm", "crt_write_pfm", "crt_checkpoint_save", "crt_checkpoint_load"]
+                 "crt_write_ppm", "crt_write_pfm", "crt_checkpoint_save", "crt_checkpoint_load",
+                 "crt_comm_unique_id", "crt_comm_init", "crt_comm_destroy", "crt_comm_info", "crt_reduce_accum",
+                 "crt_group_create", "crt_group_destroy", "crt_group_last_error", "crt_group_size", "crt_group_ctx",
+                 "crt_group_set_scene", "crt_group_set_camera", "crt_group_init_rng", "crt_group_render", "crt_group_get_stats"]
+COMM_ID_BYTES = 128
+GROUP_FORCE_NCCL = 1
 
 
 class SceneHandle:
@@ -231,9 +251,13 @@ def make_scene_struct(positions, indices, tri_material, spheres, sphere_material
 class Renderer:
     """CUDARenderer-shaped wrapper of a crt_ctx (reference: src/CUDARenderer.cuh:9-29)."""
 
-    def __init__(self, width, height, device=0, mode=MODE_WAVEFRONT, bvh_leaf_max=0):
+    def __init__(self, width, height, device=0, mode=MODE_WAVEFRONT, bvh_leaf_max=0, borrowed_ctx=None):
         self.lib = load_library()
         self.width, self.height = int(width), int(height)
+        self._borrowed = borrowed_ctx is not None
+        if self._borrowed:                      # a context owned by a DeviceGroup
+            self._ctx = C.c_void_p(borrowed_ctx)
+            return
         cfg = Config(width=self.width, height=self.height, device=device, mode=mode, bvh_leaf_max=bvh_leaf_max)
         self._ctx = C.c_void_p()
         rc = self.lib.crt_create(C.byref(self._ctx), C.byref(cfg))
@@ -332,10 +356,99 @@ class Renderer:
     def checkpoint_load(self, path):
         self._check(self.lib.crt_checkpoint_load(self._ctx, path.encode()))
 
+    # ---- multi-GPU, one process per GPU ----
+    def comm_init(self, unique_id, nranks, rank):
+        """crt_comm_init: unique_id = the 128 bytes rank 0 got from comm_unique_id()."""
+        buf = (C.c_char * COMM_ID_BYTES).from_buffer_copy(bytes(unique_id))
+        self._check(self.lib.crt_comm_init(self._ctx, C.cast(buf, C.c_void_p), int(nranks), int(rank)))
+
+    def comm_info(self):
+        n, r, v = C.c_int32(), C.c_int32(), C.c_int32()
+        self._check(self.lib.crt_comm_info(self._ctx, C.byref(n), C.byref(r), C.byref(v)))
+        return n.value, r.value, v.value
+
+    def reduce_accum(self, root=0):
+        self._check(self.lib.crt_reduce_accum(self._ctx, int(root)))
+
+    def comm_destroy(self):
+        self._check(self.lib.crt_comm_destroy(self._ctx))
+
     def close(self):
-        if self._ctx is not None and self._ctx.value:
+        if self._ctx is not None and self._ctx.value and not self._borrowed:
             self.lib.crt_destroy(self._ctx)
         self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def comm_unique_id():
+    """crt_comm_unique_id (ncclGetUniqueId): 128 bytes for rank 0 to hand to the other ranks."""
+    lib = load_library()
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    rc = lib.crt_comm_unique_id(C.cast(buf, C.c_void_p), COMM_ID_BYTES)
+    if rc != CRT_OK:
+        raise CrtError(rc, lib.crt_last_error(None).decode(errors="replace"))
+    return buf.raw
+
+
+class DeviceGroup:
+    """crt_group_*: several GPUs driven from one process; device devices[0] ends up with the frame."""
+
+    def __init__(self, width, height, devices, mode=MODE_WAVEFRONT, bvh_leaf_max=0):
+        self.lib = load_library()
+        self.width, self.height = int(width), int(height)
+        cfg = Config(width=self.width, height=self.height, device=0, mode=mode, bvh_leaf_max=bvh_leaf_max)
+        devs = (C.c_int32 * len(devices))(*[int(d) for d in devices])
+        self._g = C.c_void_p()
+        rc = self.lib.crt_group_create(C.byref(self._g), C.byref(cfg), devs, len(devices))
+        if rc != CRT_OK:
+            self._g = None
+            raise CrtError(rc, self.lib.crt_last_error(None).decode(errors="replace"))
+
+    def _check(self, rc):
+        if rc != CRT_OK:
+            raise CrtError(rc, self.lib.crt_group_last_error(self._g).decode(errors="replace"))
+
+    def size(self):
+        return self.lib.crt_group_size(self._g)
+
+    def renderer(self, index):
+        """The context of device `index` as a (borrowed) Renderer: read-backs, stats."""
+        ctx = self.lib.crt_group_ctx(self._g, int(index))
+        if not ctx:
+            raise IndexError(index)
+        return Renderer(self.width, self.height, borrowed_ctx=ctx)
+
+    def set_scene(self, scene):
+        ptr = scene.pointer() if isinstance(scene, SceneHandle) else C.pointer(scene)
+        self._check(self.lib.crt_group_set_scene(self._g, ptr))
+
+    def update_camera(self, camera):
+        self._check(self.lib.crt_group_set_camera(self._g, C.byref(camera)))
+
+    def initialize(self, seed=REFERENCE_SEED):
+        self._check(self.lib.crt_group_init_rng(self._g, int(seed)))
+
+    def render(self, spp, max_bounces=20, min_bounces=3, rr_max_prob=0.95, flags=0, group_flags=0):
+        p = RenderParams(spp=int(spp), max_bounces=int(max_bounces), min_bounces=int(min_bounces),
+                         rr_max_prob=float(rr_max_prob), flags=int(flags))
+        self._check(self.lib.crt_group_render(self._g, C.byref(p), int(group_flags)))
+        return self.stats()
+
+    def stats(self):
+        s, ms, peer = Stats(), C.c_float(), C.c_int32()
+        self._check(self.lib.crt_group_get_stats(self._g, C.byref(s), C.byref(ms), C.byref(peer)))
+        s.reduce_ms, s.peer = ms.value, bool(peer.value)
+        return s
+
+    def close(self):
+        if self._g is not None and self._g.value:
+            self.lib.crt_group_destroy(self._g)
+        self._g = None
 
     def __del__(self):
         try:

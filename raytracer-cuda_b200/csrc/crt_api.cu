@@ -14,37 +14,12 @@
 
 #include "../../include/crt_api.h"
 #include "crt_camera_host.h"
+#include "crt_ctx.h"
 #include "crt_internal.h"
 #include "crt_trace.h"
 #include "scene_gen.h"
 
 using namespace crt;
-
-struct crt_ctx {
-    crt_config cfg{};
-    int num_sms = 148;
-    cudaStream_t stream = nullptr;
-    cudaStream_t own_stream = nullptr;   // created by crt_create; `stream` may be replaced by crt_set_stream
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    // frame buffers
-    FrameBuffers fb{};
-    bool rng_ready = false;
-    // scene
-    float* d_pos = nullptr;
-    uint32_t* d_idx = nullptr;
-    int32_t* d_trimat = nullptr;
-    float* d_sph = nullptr;
-    int32_t* d_sphmat = nullptr;
-    MatRec* d_mats = nullptr;
-    uint32_t num_mats = 0;
-    WideBvh bvh{};
-    bool scene_ready = false;
-    Camera cam{};
-    bool cam_ready = false;
-    WavefrontState* wf = nullptr;
-    crt_stats stats{};
-    std::string err;
-};
 
 static std::string g_create_error = "";
 
@@ -138,6 +113,7 @@ void crt_destroy(crt_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->cfg.device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    crt_comm_release_(ctx);
     free_scene(ctx);
     wavefront_destroy(ctx->wf);
     cudaFree(ctx->fb.rng); cudaFree(ctx->fb.accum); cudaFree(ctx->fb.rgba8); cudaFree(ctx->fb.counters);

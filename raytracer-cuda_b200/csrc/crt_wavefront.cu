@@ -616,8 +616,8 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
 // the 32 entries a warp takes per trip are 32 CONSECUTIVE pixels: their A, B, C records are three contiguous
 // 512-byte runs and their six RNG words six contiguous 128-byte runs. One lane hands those nine runs to the
 // bulk asynchronous copy engine (cp.async.bulk global -> shared, completion counted on an mbarrier; the 1-D form
-// of TMA) ONE TRIP AHEAD, into the other of the warp's two 2304-byte stages; the lanes then read their entry
-// from shared memory. The per-thread version above issues 9 dependent loads + 9 L2 prefetches per entry and
+// of TMA) ONE TRIP AHEAD, into the warp's 2304-byte stage: a trip first moves its entries from the stage to
+// registers, then refills the stage for the next trip and computes while the copy runs. The per-thread version above issues 9 dependent loads + 9 L2 prefetches per entry and
 // still starts every trip with an L2 round trip; here the state of the next trip is already on the SM when
 // the trip begins, and the load/prefetch/address instructions are gone. Each warp owns its stages and
 // barriers: no CTA-wide synchronisation, warps drift apart as their rejection loops dictate.
@@ -649,30 +649,30 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
 }
 
 __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade_bulk(RenderArgs a, WfView w, uint32_t* queue, uint32_t* qcount, int cur, int par) {
-    __shared__ __align__(128) unsigned char stages[8][2][CRT_SHADE_STAGE_BYTES];
-    __shared__ __align__(8) unsigned long long bars[8][2];
+    __shared__ __align__(128) unsigned char stages[8][CRT_SHADE_STAGE_BYTES];   // one stage per warp
+    __shared__ __align__(8) unsigned long long bars[8];
     const uint32_t count = qcount[cur];
     const uint32_t rounded = (count + 31u) & ~31u;
     const size_t n = (size_t)a.rc.width * a.rc.height;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t first = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
     const bool planes_aligned = (n & 3u) == 0u;   // every RNG plane starts on a 16-byte boundary
-    const uint32_t bar0 = smem_addr(&bars[warp][0]), stage0 = smem_addr(&stages[warp][0][0]);
+    const uint32_t bar = smem_addr(&bars[warp]), dst = smem_addr(&stages[warp][0]);
+    const unsigned char* sb = &stages[warp][0];
     if (lane == 0) {
-        mbar_init(bar0, 1u);
-        mbar_init(bar0 + 8u, 1u);
+        mbar_init(bar, 1u);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    uint32_t phase_bits = 0u, bulk_bits = 0u;   // per stage: parity to wait for / the stage was filled by the copy engine (warp-uniform)
-    // the warp's queue words of this trip, the next and the one after (64-bit index: first + 2*stride may pass 2^32)
+    uint32_t phase = 0u;     // parity of the barrier phase the next bulk load completes (warp-uniform)
     auto queue_word = [&](unsigned long long i) -> uint32_t { return i < (unsigned long long)count ? queue[i] : QUEUE_DEAD; };
-    auto issue = [&](uint32_t st, uint32_t qw) {
+    // Start the copy of the 32 entries `qw` (one per lane) into the warp's stage when they are one aligned run of
+    // pixels; otherwise prefetch them into L2 for the per-thread loads of the next trip. True = the stage is filling.
+    auto issue = [&](uint32_t qw) -> bool {
         const uint32_t qbase = __shfl_sync(0xffffffffu, qw, 0);
         const bool run = __all_sync(0xffffffffu, qw != QUEUE_DEAD && qw == qbase + lane) && planes_aligned && (qbase & 3u) == 0u;
         if (run) {
             if (lane == 0) {
-                const uint32_t bar = bar0 + 8u * st, dst = stage0 + CRT_SHADE_STAGE_BYTES * st;
                 mbar_expect_tx(bar, CRT_SHADE_STAGE_BYTES);
                 bulk_g2s(dst, w.A + qbase, 512u, bar);
                 bulk_g2s(dst + 512u, w.B + qbase, 512u, bar);
@@ -680,36 +680,30 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade_bulk(Ren
 #pragma unroll
                 for (uint32_t k = 0; k < 6u; k++) bulk_g2s(dst + 1536u + 128u * k, a.fb.rng + (size_t)k * n + qbase, 128u, bar);
             }
-            bulk_bits |= 1u << st;
-        } else {
-            bulk_bits &= ~(1u << st);
-            if (qw != QUEUE_DEAD) {
-                asm volatile("prefetch.global.L2 [%0];" :: "l"(w.A + qw));
-                asm volatile("prefetch.global.L2 [%0];" :: "l"(w.B + qw));
-                asm volatile("prefetch.global.L2 [%0];" :: "l"(w.C + qw));
+        } else if (qw != QUEUE_DEAD) {
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(w.A + qw));
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(w.B + qw));
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(w.C + qw));
 #pragma unroll
-                for (int k = 0; k < 6; k++) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.fb.rng + (size_t)k * n + qw));
-            }
+            for (int k = 0; k < 6; k++) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.fb.rng + (size_t)k * n + qw));
         }
         if (qw != QUEUE_DEAD) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.fb.accum + qw));   // read only when a path ends
+        return run;
     };
+    // the warp's queue words of this trip and the next (64-bit index: first + 2*stride may pass 2^32)
     uint32_t q_cur = queue_word(first), q_next = queue_word((unsigned long long)first + stride);
-    if (first < rounded) issue(0u, q_cur);
-    uint32_t st = 0u;
-    for (uint32_t i = first; i < rounded; st ^= 1u) {
+    bool staged = first < rounded ? issue(q_cur) : false;
+    for (uint32_t i = first; i < rounded;) {
         const uint32_t pix = q_cur;
         const unsigned long long i_next = (unsigned long long)i + stride;
         const uint32_t q_after = queue_word(i_next + stride);
-        // the other stage was read to registers in the last trip (a __syncwarp ago): refill it for the next one
-        if (i_next < (unsigned long long)rounded) issue(st ^ 1u, q_next);
         float4 A, B, C;
         Rng rng;
         A = B = C = make_float4(0.f, 0.f, 0.f, 0.f);
         rng.v0 = rng.v1 = rng.v2 = rng.v3 = rng.v4 = rng.d = 0u;
-        if ((bulk_bits >> st) & 1u) {
-            mbar_wait(bar0 + 8u * st, (phase_bits >> st) & 1u);
-            phase_bits ^= 1u << st;
-            const unsigned char* sb = &stages[warp][st][0];
+        if (staged) {
+            mbar_wait(bar, phase);
+            phase ^= 1u;
             A = reinterpret_cast<const float4*>(sb)[lane];
             B = reinterpret_cast<const float4*>(sb + 512)[lane];
             C = reinterpret_cast<const float4*>(sb + 1024)[lane];
@@ -720,7 +714,10 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade_bulk(Ren
             A = w.A[pix]; B = w.B[pix]; C = w.C[pix];
             rng = wf_load_rng(a.fb.rng, n, pix);
         }
+        // every lane holds its entry in registers: the stage is free again, and the next trip's entries start to
+        // arrive while this trip computes
         __syncwarp();
+        staged = i_next < (unsigned long long)rounded ? issue(q_next) : false;
         if (pix != QUEUE_DEAD && C.x != PARKED_T) {   // a parked pixel waits for extend to finish its ray: nothing is touched
             vec3 o = mk3(A.x, A.y, A.z), d = mk3(B.x, B.y, B.z), thr = mk3(fabsf(A.w), B.w, C.z);   // |A.w|: PARKED_SIGN may be left on it
             const uint32_t book = __float_as_uint(C.w);
