@@ -183,7 +183,7 @@ def kernel_rooflines(args, kst, st_counted, build, peaks, l2_gbs, traffic_json, 
     rows = []
 
     def row(name, bound, peak, nbytes, ms, launches, model, extra=None):
-        ach = nbytes / (ms * 1e-3) / 1e9 if ms and ms > 0 else None
+        ach = nbytes / (ms * 1e-3) / 1e9 if (nbytes and ms and ms > 0) else None
         r = {"kernel": name, "bound": bound, "bytes_model": model, "algorithmic_bytes": nbytes, "ms": ms, "launches": launches,
              "achieved_gbs": ach, "peak_gbs": peak, "frac": (ach / peak) if (ach and peak) else None}
         tj = traffic_json.get(name)
@@ -295,7 +295,7 @@ def main():
     def timed(n, **kw):
         """n steps bracketed by barrier + synchronize, timed with CUDA events on the launching stream."""
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        acc = {"rays": 0, "launches": 0, "host_syncs": 0, "iterations": 0, "last": None}
+        acc = {"rays": 0, "launches": 0, "host_syncs": 0, "iterations": 0, "graphs": 0, "last": None}
         sync_all()
         ev0.record(stream)
         for _ in range(n):
@@ -304,6 +304,7 @@ def main():
             acc["launches"] += int(st.kernel_launches) + (1 if world > 1 and rank == 0 else 0)
             acc["host_syncs"] += int(st.host_syncs)
             acc["iterations"] += int(st.iterations)
+            acc["graphs"] += int(st.graph_launches)
             acc["last"] = st
         ev1.record(stream)
         sync_all()
@@ -421,6 +422,7 @@ def main():
                         "d2h_bytes_per_step": W * H * 4, "ms_per_step": dt_e2e / args.steps * 1e3},
                 "gpu_launches": int(launches_all), "launches_per_frame": launches_all / args.steps / world,
                 "host_syncs_per_frame": syncs_all / args.steps / world, "iterations_per_frame": main_run["iterations"] / args.steps,
+                "graph_launches_per_frame": main_run["graphs"] / args.steps,
                 "check": check, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())

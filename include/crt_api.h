@@ -175,7 +175,9 @@ typedef struct crt_stats {
     float    compact_ms;       /* wavefront, with CRT_RENDER_TIME_KERNELS: the k_compact_* triples                    */
     uint32_t host_syncs;       /* blocking stream synchronisations inside the last crt_render (queue-length read-backs) */
     uint32_t iterations;       /* wavefront iterations (extend + shade per part) of the last crt_render               */
-    uint64_t reserved[1];
+    uint32_t graph_launches;   /* batches of the last crt_render replayed as one CUDA graph launch (their kernels are
+                                  counted in kernel_launches all the same)                                             */
+    uint32_t reserved[1];
 } crt_stats;
 
 typedef struct crt_ctx crt_ctx;

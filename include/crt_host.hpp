@@ -268,6 +268,62 @@ private:
     int m_Width, m_Height;
 };
 
+// CUDARenderer over several GPUs of this process (crt_group_*): same calls; a frame's samples are sharded
+// over the devices and the root device (devices[0]) ends up with the summed buffer and the image. The reference has
+// nothing like it (one device: CUDARenderer.cuh:55-60).
+class CUDARendererGroup {
+public:
+    CUDARendererGroup(int width, int height, const std::vector<int>& devices, int mode = CRT_MODE_AUTO) : m_Width(width), m_Height(height) {
+        crt_config cfg = {};
+        cfg.width = width; cfg.height = height; cfg.mode = mode;
+        std::vector<int32_t> d(devices.begin(), devices.end());
+        const int rc = crt_group_create(&m_Group, &cfg, d.data(), (int32_t)d.size());
+        if (rc != CRT_OK) {
+            std::string why = crt_last_error(nullptr);
+            if (why.empty()) why = errorName(rc);
+            throw std::runtime_error("CUDA error: " + why + " (code " + std::to_string(rc) + ")");
+        }
+    }
+    CUDARendererGroup(const CUDARendererGroup&) = delete;
+    CUDARendererGroup& operator=(const CUDARendererGroup&) = delete;
+    ~CUDARendererGroup() { crt_group_destroy(m_Group); }
+    void initialize(unsigned long long seed = 1804289383ull) { check(crt_group_init_rng(m_Group, seed)); }
+    void setScene(const SceneManager& scene) {
+        if (!scene.getWorld()) throw std::runtime_error("setScene: the SceneManager holds no scene");
+        check(crt_group_set_scene(m_Group, scene.getWorld()));
+    }
+    void updateCamera(const Camera& camera) { const crt_camera c = camera.toApi(); check(crt_group_set_camera(m_Group, &c)); }
+    void render(int samplesPerPixel, int maxBounces = 20, unsigned flags = 0, unsigned groupFlags = 0) {
+        crt_render_params p = {};
+        p.spp = samplesPerPixel; p.max_bounces = maxBounces; p.min_bounces = 3; p.rr_max_prob = 0.95f; p.flags = flags;
+        check(crt_group_render(m_Group, &p, groupFlags));
+    }
+    void copyImageToHost(unsigned char* hostRgba8) const { checkRoot(crt_get_image_rgba8(root(), hostRgba8, nullptr)); }
+    void copyAccumToHost(float* hostRgba32f) const { checkRoot(crt_get_accum(root(), hostRgba32f, nullptr)); }
+    crt_stats stats(float* reduceMs = nullptr, bool* peer = nullptr) const {
+        crt_stats s = {};
+        int32_t p = 0;
+        check(crt_group_get_stats(m_Group, &s, reduceMs, &p));
+        if (peer) *peer = p != 0;
+        return s;
+    }
+    crt_stats rootStats() const { crt_stats s = {}; checkRoot(crt_get_stats(root(), &s)); return s; }
+    void writePPM(const std::string& path) const { checkRoot(crt_write_ppm(root(), path.c_str())); }
+    void writePFM(const std::string& path) const { checkRoot(crt_write_pfm(root(), path.c_str())); }
+    int size() const { return crt_group_size(m_Group); }
+    crt_ctx* root() const { return crt_group_ctx(m_Group, 0); }
+
+private:
+    void check(int rc) const {
+        if (rc != CRT_OK) throw std::runtime_error(std::string("CUDA error: ") + crt_group_last_error(m_Group) + " (code " + std::to_string(rc) + ")");
+    }
+    void checkRoot(int rc) const {
+        if (rc != CRT_OK) throw std::runtime_error(std::string("CUDA error: ") + crt_last_error(root()) + " (code " + std::to_string(rc) + ")");
+    }
+    crt_group* m_Group = nullptr;
+    int m_Width, m_Height;
+};
+
 // WindowManager::drawFrame without the window (WindowManager.h:79-93): device image -> host, flipVertically.
 class WindowManager {
 public:

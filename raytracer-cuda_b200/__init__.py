@@ -64,7 +64,7 @@ class Stats(C.Structure):
                 ("nodes_fetched", C.c_uint64), ("prims_tested", C.c_uint64), ("extend_ms", C.c_float), ("shade_ms", C.c_float),
                 ("extend_launches", C.c_uint32), ("shade_launches", C.c_uint32), ("bvh_giants", C.c_uint32),
                 ("tail_ms", C.c_float), ("begin_ms", C.c_float), ("compact_ms", C.c_float), ("host_syncs", C.c_uint32),
-                ("iterations", C.c_uint32), ("reserved", C.c_uint64 * 1)]
+                ("iterations", C.c_uint32), ("graph_launches", C.c_uint32), ("reserved", C.c_uint32 * 1)]
 
 
 class CrtError(RuntimeError):

@@ -260,7 +260,7 @@ static int render_impl(crt_ctx* ctx, const crt_render_params* p, bool counted) {
     if (mega) { kt.extend_ms = ctx->stats.render_ms; kt.extend_launches = 1; }
     ctx->stats.extend_ms = kt.extend_ms; ctx->stats.shade_ms = kt.shade_ms; ctx->stats.tail_ms = kt.tail_ms;
     ctx->stats.extend_launches = kt.extend_launches; ctx->stats.shade_launches = kt.shade_launches;
-    ctx->stats.begin_ms = kt.begin_ms; ctx->stats.compact_ms = kt.compact_ms; ctx->stats.host_syncs = kt.host_syncs + 1u; ctx->stats.iterations = kt.iterations;
+    ctx->stats.begin_ms = kt.begin_ms; ctx->stats.compact_ms = kt.compact_ms; ctx->stats.host_syncs = kt.host_syncs + 1u; ctx->stats.iterations = kt.iterations; ctx->stats.graph_launches = kt.graph_launches;
     if (incomplete) return fail(ctx, CRT_E_LIMIT, "crt_render: iteration bound reached with pixels still unfinished (frame incomplete)");
     return CRT_OK;
 }

@@ -18,7 +18,7 @@ namespace {
 
 struct Options {
     std::string scene = "cornell", obj, ppm, pfm, trace;
-    int param = 0, width = 800, height = 600, spp = 0, bounces = 20, frames = 1, mode = CRT_MODE_AUTO, hq_spp = CRT::HIGH_QUALITY_SAMPLES_PER_PIXEL;
+    int param = 0, width = 800, height = 600, spp = 0, bounces = 20, frames = 1, gpus = 1, force_nccl = 0, mode = CRT_MODE_AUTO, hq_spp = CRT::HIGH_QUALITY_SAMPLES_PER_PIXEL;
     unsigned long long seed = 1804289383ull;
     float orbit = 0.f, vfov = 90.f, aperture = 0.f;   // EntryPoint.cu:11-12 defaults
 };
@@ -27,9 +27,11 @@ void usage() {
     std::printf("usage: crt_cli [--scene cornell|cornell_blob|spheres|terrain] [--param N] [--obj a.obj[,b.obj]]\n"
                 "               [--width W] [--height H] [--spp N] [--bounces B] [--frames F] [--orbit DEG_PER_FRAME]\n"
                 "               [--mode wavefront|megakernel|auto] [--seed S] [--hq-spp N] [--ppm FILE] [--pfm FILE]\n"
-                "               [--controller-trace SCRIPT]\n"
+                "               [--controller-trace SCRIPT] [--gpus N] [--nccl]\n"
                 "  --spp N            one still frame of N samples per pixel (the reference's high-quality frame)\n"
                 "  --frames F         F progressive frames through Raytracer::run (1 spp while the camera moves)\n"
+                "  --gpus N           with --spp: shard the frame's samples over GPUs 0..N-1 of this process (crt_group_*)\n"
+                "  --nccl             with --gpus: reduce with ncclReduce instead of the peer-memory kernel\n"
                 "  --controller-trace print the camera pose after every scripted frame; host logic only, no GPU\n");
 }
 
@@ -95,6 +97,25 @@ int run(const Options& o) {
         const CRT::Vec3 position(0, 4, 4), target(0, 0, 0);
         camera = CRT::Camera((float)o.width / (float)o.height, o.vfov, position, target, CRT::Vec3(0, 1, 0), o.aperture, (position - target).length());
     }
+    if (o.gpus > 1) {   // one still frame over several GPUs: the spp budget sharded, one reduce onto GPU 0
+        if (o.spp <= 0) throw std::runtime_error("--gpus needs --spp (a still frame); progressive 1-spp frames do not shard");
+        std::vector<int> devices;
+        for (int d = 0; d < o.gpus; d++) devices.push_back(d);
+        CRT::CUDARendererGroup group(o.width, o.height, devices, o.mode);
+        group.initialize(o.seed);
+        group.setScene(scene);
+        group.updateCamera(camera);
+        group.render(o.spp, o.bounces, 0, o.force_nccl ? CRT_GROUP_FORCE_NCCL : 0);
+        float reduce_ms = 0.f;
+        bool peer = false;
+        const crt_stats st = group.stats(&reduce_ms, &peer);
+        if (!o.ppm.empty()) group.writePPM(o.ppm);
+        if (!o.pfm.empty()) group.writePFM(o.pfm);
+        std::printf("{\"frames\": 1, \"gpus\": %d, \"width\": %d, \"height\": %d, \"rays\": %llu, \"render_ms\": %.3f, \"reduce_ms\": %.3f, "
+                    "\"reduce\": \"%s\", \"mrays_per_s\": %.1f}\n", o.gpus, o.width, o.height, (unsigned long long)st.rays, st.render_ms, reduce_ms,
+                    peer && !o.force_nccl ? "peer-memory kernel" : "ncclReduce", st.render_ms > 0 ? st.rays / (st.render_ms + reduce_ms) / 1e3 : 0.0);
+        return 0;
+    }
     CRT::CUDARenderer renderer(o.width, o.height, o.mode);
     CRT::WindowManager window(o.width, o.height);
     renderer.initialize(o.seed);
@@ -155,6 +176,8 @@ int main(int argc, char** argv) {
         else if (a == "--ppm") o.ppm = next();
         else if (a == "--pfm") o.pfm = next();
         else if (a == "--controller-trace") o.trace = next();
+        else if (a == "--gpus") o.gpus = std::atoi(next());
+        else if (a == "--nccl") o.force_nccl = 1;
         else if (a == "--mode") { const std::string m = next(); o.mode = m == "wavefront" ? CRT_MODE_WAVEFRONT : m == "megakernel" ? CRT_MODE_MEGAKERNEL : CRT_MODE_AUTO; }
         else { std::fprintf(stderr, "unknown option %s\n", a.c_str()); usage(); return 2; }
     }

@@ -18,6 +18,7 @@
 #include <dlfcn.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -54,10 +55,16 @@ NcclApi* nccl() {
     static bool tried = false;
     if (tried) return &api;
     tried = true;
+    // 1. a copy of NCCL the process already holds (PyTorch brings its own libnccl.so.2): two NCCL versions cannot share
+    //    the soname, so that one is used. 2. CRT_NCCL_LIB (a path). 3. the system's libnccl.so.2.
+    // A process that will load PyTorch LATER should import it before the first crt_comm_* / crt_group_* call (or set
+    // CRT_NCCL_LIB to PyTorch's copy): otherwise PyTorch would find the system's older NCCL under its soname.
+    api.so = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!api.so) if (const char* path = getenv("CRT_NCCL_LIB")) api.so = dlopen(path, RTLD_NOW | RTLD_LOCAL);
     const char* names[] = {"libnccl.so.2", "libnccl.so"};
     for (const char* n : names) {
-        api.so = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
         if (api.so) break;
+        api.so = dlopen(n, RTLD_NOW | RTLD_LOCAL);
     }
     if (!api.so) { api.why = std::string("NCCL not found (dlopen libnccl.so.2): ") + (dlerror() ? dlerror() : ""); return &api; }
     bool ok = true;

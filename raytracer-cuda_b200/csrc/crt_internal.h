@@ -28,7 +28,7 @@ struct RenderArgs {
 struct KernelTimes {
     float extend_ms = 0.f, shade_ms = 0.f, tail_ms = 0.f, begin_ms = 0.f, compact_ms = 0.f;
     uint32_t extend_launches = 0, shade_launches = 0;
-    uint32_t host_syncs = 0, compactions = 0, iterations = 0;   // blocking stream synchronisations / queue compactions / wavefront iterations of the frame
+    uint32_t host_syncs = 0, compactions = 0, iterations = 0, graph_launches = 0;   // blocking stream synchronisations / queue compactions / wavefront iterations of the frame
 };
 
 // crt_render.cu — every launcher enqueues on `stream` and returns the launch error (no sync).

@@ -255,7 +255,7 @@ struct Traverser {
         const float ddx = fabsf(d.x) < tiny ? (d.x < 0.f ? -tiny : tiny) : d.x;
         const float ddy = fabsf(d.y) < tiny ? (d.y < 0.f ? -tiny : tiny) : d.y;
         const float ddz = fabsf(d.z) < tiny ? (d.z < 0.f ? -tiny : tiny) : d.z;
-        idx = 1.0f / ddx; idy = 1.0f / ddy; idz = 1.0f / ddz;
+        idx = f_rcp(ddx); idy = f_rcp(ddy); idz = f_rcp(ddz);
         octinv = (ddx < 0.f ? 0u : 4u) | (ddy < 0.f ? 0u : 2u) | (ddz < 0.f ? 0u : 1u);
         sp = 0;
         ng_x = 0u; ng_y = 0x80000000u;

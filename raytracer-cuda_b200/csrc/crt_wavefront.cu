@@ -19,6 +19,8 @@
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
+#include <vector>
 
 #include "crt_internal.h"
 #include "crt_shade.h"
@@ -50,7 +52,18 @@ struct WfPart {
     cudaEvent_t ev_done = nullptr;
 };
 
+// One batch of iterations (16 x parts x (extend, shade) + the compaction triples + the queue-length read-backs) as an
+// instantiated CUDA graph, keyed by everything its launches depend on (kernel arguments included).
+struct WfGraph {
+    std::vector<unsigned char> sig;
+    cudaGraphExec_t exec = nullptr;
+    int seen = 0;
+};
+
 struct WavefrontState {
+    std::vector<WfGraph> graphs;
+    int use_graph = 1;               // env CRT_WF_GRAPH: replay a batch whose launches were seen before as one CUDA graph launch
+    int blocked = 0;                 // env CRT_WF_BLOCKED: temporal blocking experiment, a part runs its whole batch before the next part starts (one stream)
     float4* A = nullptr;
     float4* B = nullptr;
     float4* C = nullptr;
@@ -60,7 +73,7 @@ struct WavefrontState {
     cudaEvent_t ev_fork = nullptr;
     size_t n = 0;
     int blocks_extend = 0, blocks_shade = 0;
-    int shade_bulk = 1;              // env CRT_SHADE_BULK: shade's path state arrives through cp.async.bulk (k_wf_shade_bulk); 0 = per-thread loads (k_wf_shade)
+    int shade_bulk = 0;              // env CRT_SHADE_BULK=1: shade's path state arrives through cp.async.bulk (k_wf_shade_bulk); 0 = per-thread loads (k_wf_shade). Measured equal
     int extend_reverse = 1;          // env CRT_EXTEND_REVERSE: extend consumes the queue back to front (L2 reuse of what shade just wrote)
     int fetch_lanes = CRT_FETCH_LANES, postpone_lanes = CRT_POSTPONE_LANES, coop = 0, shade_persistent = 1;   // tuning knobs (env CRT_FETCH_LANES / CRT_POSTPONE_LANES)
     int drain_rounds = 4;            // env CRT_DRAIN_ROUNDS: rounds a warp keeps going after the queue ran out, then it suspends its rays (0 = never suspend)
@@ -329,7 +342,7 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
                 const float ddx = fabsf(B.x) < tiny ? (B.x < 0.f ? -tiny : tiny) : B.x;
                 const float ddy = fabsf(B.y) < tiny ? (B.y < 0.f ? -tiny : tiny) : B.y;
                 const float ddz = fabsf(B.z) < tiny ? (B.z < 0.f ? -tiny : tiny) : B.z;
-                idx = 1.0f / ddx; idy = 1.0f / ddy; idz = 1.0f / ddz;
+                idx = f_rcp(ddx); idy = f_rcp(ddy); idz = f_rcp(ddz);   // = 1.0f / x (both correctly rounded), without the division's slow path
                 octinv = (ddx < 0.f ? 0u : 4u) | (ddy < 0.f ? 0u : 2u) | (ddz < 0.f ? 0u : 1u);
                 if (pix & PARKED_LANE) {
                     // a traversal parked by the previous extend launch: closest hit so far, node group and stack come back
@@ -554,7 +567,7 @@ __device__ __forceinline__ bool shade_step(const RenderArgs& a, uint32_t pix, ve
 
 // ---- shade: consume the hit, continue / finish / regenerate, Russian roulette, compact -----------------
 #ifndef CRT_SHADE_MIN_BLOCKS
-#define CRT_SHADE_MIN_BLOCKS 5
+#define CRT_SHADE_MIN_BLOCKS 4   // 64 registers, no spills: 6 % faster than 5 CTAs of 48 registers since the one-pass shade_step
 #endif
 __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderArgs a, WfView w, uint32_t* queue, uint32_t* qcount, int cur, int par) {
     const uint32_t count = qcount[cur];
@@ -873,6 +886,8 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
     int be = 0, bs = 0;
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&be, k_wf_extend<false, false>, CRT_EXTEND_THREADS, 0);
     if (const char* v = getenv("CRT_SHADE_BULK")) s->shade_bulk = atoi(v);
+    if (const char* v = getenv("CRT_WF_GRAPH")) s->use_graph = atoi(v);
+    if (const char* v = getenv("CRT_WF_BLOCKED")) s->blocked = atoi(v);
     if (e == cudaSuccess) e = s->shade_bulk ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade_bulk, 256, 0)
                                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade, 256, 0);
     if (const char* v = getenv("CRT_FETCH_LANES")) s->fetch_lanes = atoi(v);
@@ -909,6 +924,7 @@ void wavefront_destroy(WavefrontState* s) {
     for (cudaStream_t st : s->side_stream) if (st) cudaStreamDestroy(st);
     if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     for (cudaEvent_t ev : s->ev) if (ev) cudaEventDestroy(ev);
+    for (WfGraph& g : s->graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
     delete s;
 }
 
@@ -944,17 +960,17 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
             e = cudaMalloc(&q.suspended[k], (size_t)grid_e * CRT_EXTEND_THREADS * CRT_SUSPEND_WORDS * sizeof(uint2));
         // per-kernel times only mean something when the kernels run one after the other: a timed render keeps
         // the same launches (one per part) but puts them all on the caller's stream
-        q.stream = (p == 0 || timed) ? stream : ws->side_stream[p];
+        q.stream = (p == 0 || timed || ws->blocked) ? stream : ws->side_stream[p];
         bq.queue[p] = q.queue[0]; bq.qcount[p] = q.qcount; bq.cap[p] = q.cap;
     }
     if (e != cudaSuccess) return e;
-    uint32_t nl = 0, compactions = 0, host_syncs = 0;
+    uint32_t nl = 0, compactions = 0, host_syncs = 0, nl_graph = 0;
     if (timed) cudaEventRecord(ws->ev[ev_begin], stream);
     k_wf_begin<<<grid_s, 256, 0, stream>>>(a, w, bq);
     if (timed) cudaEventRecord(ws->ev[ev_begin + 1], stream);
     nl++;
     e = cudaGetLastError();
-    if (e == cudaSuccess && parts > 1 && !timed) {
+    if (e == cudaSuccess && parts > 1 && !timed && !ws->blocked) {
         e = cudaEventRecord(ws->ev_fork, stream);
         for (int p = 1; p < parts && e == cudaSuccess; p++) e = cudaStreamWaitEvent(ws->side_stream[p], ws->ev_fork, 0);
     }
@@ -974,8 +990,57 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         // when no ray gets parked (one iteration per path segment), and short batches for the stragglers after that
         const long long needed = (long long)a.rc.spp * a.rc.max_bounces + 1 - it;
         const int nb = needed >= batch ? batch : (needed > 0 ? (int)needed : 4);
-        for (int b = 0; b < nb; b++) {
+        // ---- CUDA graph of the batch -------------------------------------------------------------------------
+        // The launches of a batch depend on a handful of host-side facts (which queue is current, the parity of the
+        // parked-ray lists, whether rays are parked at all) and on the kernel arguments. For ~85 % of a long frame
+        // these repeat from batch to batch, so the batch is captured once (the second time its signature is seen:
+        // a frame whose camera moves every frame never pays for an instantiation) and replayed with ONE launch:
+        // 70 launches + 2 stream joins become one cudaGraphLaunch and one synchronisation.
+        bool graphable = ws->use_graph && !timed && !counted && !ws->coop;
+        for (int p = 0; p < parts; p++) if (!ws->part[p].done && ws->part[p].tail) graphable = false;   // tail grids follow the queue length
+        WfGraph* graph = nullptr;
+        bool capture = false;
+        if (graphable) {
+            std::vector<unsigned char> sig(sizeof(RenderArgs) + sizeof(WfView) + 64, 0);
+            memcpy(sig.data(), &a, sizeof(RenderArgs));
+            memcpy(sig.data() + sizeof(RenderArgs), &w, sizeof(WfView));
+            unsigned char* t = sig.data() + sizeof(RenderArgs) + sizeof(WfView);
+            *t++ = (unsigned char)nb; *t++ = (unsigned char)parts; *t++ = (unsigned char)ws->blocked; *t++ = (unsigned char)ws->shade_bulk;
+            *t++ = (unsigned char)ws->fetch_lanes; *t++ = (unsigned char)ws->drain_rounds; *t++ = (unsigned char)ws->extend_reverse; *t++ = (unsigned char)ws->shade_persistent;
             for (int p = 0; p < parts; p++) {
+                const WfPart& q = ws->part[p];
+                *t++ = (unsigned char)q.done; *t++ = (unsigned char)q.cur; *t++ = (unsigned char)(q.extend_launches & 1u);
+                *t++ = (unsigned char)((suspend && (long long)q.live >= min_live) ? 1 : 0);
+            }
+            memcpy(t, &stream, sizeof(stream));
+            for (WfGraph& g : ws->graphs) if (g.sig == sig) { graph = &g; break; }
+            if (!graph) {
+                if (ws->graphs.size() >= 32) {   // bounded: drop the oldest
+                    if (ws->graphs.front().exec) cudaGraphExecDestroy(ws->graphs.front().exec);
+                    ws->graphs.erase(ws->graphs.begin());
+                }
+                ws->graphs.emplace_back();
+                graph = &ws->graphs.back();
+                graph->sig = sig;
+            }
+            graph->seen++;
+            capture = !graph->exec && graph->seen >= 2;
+        }
+        const bool replay = graph && graph->exec;
+        const bool emit = !replay;   // launches are issued (directly, or into the capture); bookkeeping always runs
+        if (capture) {
+            e = cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal);
+            if (e == cudaSuccess && parts > 1 && !ws->blocked) {
+                e = cudaEventRecord(ws->ev_fork, stream);
+                for (int p = 1; p < parts && e == cudaSuccess; p++) e = cudaStreamWaitEvent(ws->side_stream[p], ws->ev_fork, 0);
+            }
+            if (e != cudaSuccess) break;
+        }
+        const int slots = nb * parts;
+        for (int k = 0; k < slots; k++) {
+            // iteration-major: the parts alternate (their kernels overlap on two streams); CRT_WF_BLOCKED: part-major
+            const int b = ws->blocked ? k % nb : k / parts, p = ws->blocked ? k / nb : k % parts;
+            {
                 WfPart& q = ws->part[p];
                 if (q.done) continue;
                 cudaStream_t st = q.stream;
@@ -990,7 +1055,7 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                     }
                     // spread the pixels over the warps the machine holds (shared by the parts that are in their tail)
                     int tail_parts = 0;
-                    for (int k = 0; k < parts; k++) tail_parts += (!ws->part[k].done && ws->part[k].tail) ? 1 : 0;
+                    for (int k2 = 0; k2 < parts; k2++) tail_parts += (!ws->part[k2].done && ws->part[k2].tail) ? 1 : 0;
                     const long long warps_resident = (long long)num_sms * ws->tail_blocks * (CRT_TAIL_THREADS / 32) / (tail_parts > 0 ? tail_parts : 1);
                     long long lanes = ((long long)q.live + warps_resident - 1) / (warps_resident > 0 ? warps_resident : 1);
                     if (lanes < ws->tail_lanes_min) lanes = ws->tail_lanes_min;
@@ -1007,6 +1072,8 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                 const int shade_grid = ws->shade_persistent ? grid_s : (int)((q.live + 255u) / 256u);
                 const int drain = (suspend && (long long)q.live >= min_live) ? ws->drain_rounds : 0;
                 const int par = (int)(q.extend_launches++ & 1u);
+                nl += 2;
+                if (!emit) continue;
                 if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p)], st);
                 if (counted) k_wf_extend<true, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
                 else if (ws->coop) k_wf_extend<false, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
@@ -1015,32 +1082,56 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                 if (ws->shade_bulk) k_wf_shade_bulk<<<shade_grid, 256, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur, par);
                 else k_wf_shade<<<shade_grid, 256, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur, par);
                 if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p) + 2], st);
-                nl += 2;
             }
-            it++;
         }
+        it += nb;
         // order-preserving compaction of the survivors into the other queue, then the new length comes back
         for (int p = 0; p < parts; p++) {
             WfPart& q = ws->part[p];
             if (q.done) continue;
-            const int tiles = (int)((q.live + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE);
-            if (timed) cudaEventRecord(ws->ev[ev_begin + 2 + 2 * CRT_WF_MAX_PARTS + 2 * p], q.stream);
-            k_compact_count<<<tiles, 256, 0, q.stream>>>(q.queue[q.cur], q.qcount, q.cur, q.tile_count);
-            k_compact_scan<<<1, 1024, 0, q.stream>>>(q.tile_count, tiles, q.qcount, q.cur);
-            k_compact_scatter<<<tiles, 256, 0, q.stream>>>(q.queue[q.cur], q.queue[q.cur ^ 1], q.qcount, q.cur, q.tile_count);
-            if (timed) cudaEventRecord(ws->ev[ev_begin + 3 + 2 * CRT_WF_MAX_PARTS + 2 * p], q.stream);
+            // a graph keeps its grids: sized for the part's capacity (CTAs past the queue's end return at once)
+            const int tiles = (int)(((graphable ? q.cap : q.live) + CRT_COMPACT_TILE - 1) / CRT_COMPACT_TILE);
             nl += 3;
             compactions++;
+            if (emit) {
+                if (timed) cudaEventRecord(ws->ev[ev_begin + 2 + 2 * CRT_WF_MAX_PARTS + 2 * p], q.stream);
+                k_compact_count<<<tiles, 256, 0, q.stream>>>(q.queue[q.cur], q.qcount, q.cur, q.tile_count);
+                k_compact_scan<<<1, 1024, 0, q.stream>>>(q.tile_count, tiles, q.qcount, q.cur);
+                k_compact_scatter<<<tiles, 256, 0, q.stream>>>(q.queue[q.cur], q.queue[q.cur ^ 1], q.qcount, q.cur, q.tile_count);
+                if (timed) cudaEventRecord(ws->ev[ev_begin + 3 + 2 * CRT_WF_MAX_PARTS + 2 * p], q.stream);
+            }
             q.cur ^= 1;
-            cudaMemcpyAsync(q.h_qcount, q.qcount, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, q.stream);
+            if (emit) cudaMemcpyAsync(q.h_qcount, q.qcount, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, q.stream);
         }
-        e = cudaGetLastError();
+        if (capture) {
+            // join the side streams, close the capture, instantiate
+            for (int p = 1; p < parts && e == cudaSuccess; p++) {
+                WfPart& q = ws->part[p];
+                if (q.stream == stream) continue;
+                e = cudaEventRecord(q.ev_done, q.stream);
+                if (e == cudaSuccess) e = cudaStreamWaitEvent(stream, q.ev_done, 0);
+            }
+            cudaGraph_t g = nullptr;
+            const cudaError_t e2 = cudaStreamEndCapture(stream, &g);
+            if (e == cudaSuccess) e = e2;
+            if (e == cudaSuccess) e = cudaGraphInstantiate(&graph->exec, g, 0);
+            if (g) cudaGraphDestroy(g);
+            if (e != cudaSuccess) break;
+        }
+        if (graph && graph->exec) {
+            e = cudaGraphLaunch(graph->exec, stream);
+            nl_graph++;
+            if (e == cudaSuccess) { e = cudaStreamSynchronize(stream); host_syncs++; }   // the side branches joined `stream` inside the graph
+        }
+        if (e == cudaSuccess) e = cudaGetLastError();
         for (int p = 0; p < parts && e == cudaSuccess; p++) {
             WfPart& q = ws->part[p];
             if (q.done) continue;
-            e = cudaStreamSynchronize(q.stream);
-            host_syncs++;
-            if (e != cudaSuccess) break;
+            if (!(graph && graph->exec)) {
+                e = cudaStreamSynchronize(q.stream);
+                if (p == 0 || q.stream != stream) host_syncs++;
+                if (e != cudaSuccess) break;
+            }
             q.live = q.h_qcount[q.cur];
             if (q.live == 0u) q.done = true; else active++;
         }
@@ -1084,7 +1175,7 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         for (int p = 0; p < parts; p++) if (!ws->part[p].done) *incomplete = true;
     }
     if (launches) *launches += nl;
-    if (times) { times->host_syncs += host_syncs; times->compactions += compactions; times->iterations += (uint32_t)it; }
+    if (times) { times->host_syncs += host_syncs; times->compactions += compactions; times->iterations += (uint32_t)it; times->graph_launches += nl_graph; }
     return e;
 }
 

@@ -8,6 +8,7 @@ import sys
 
 import numpy as np
 import pytest
+import torch   # BEFORE the library binds NCCL: PyTorch's libnccl.so.2 must be the one in the process (crt_comm.cu, nccl())
 
 pytestmark = pytest.mark.gpu
 SEED = 1804289383
@@ -15,7 +16,6 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _device_count():
-    import torch
     return torch.cuda.device_count()
 
 

@@ -99,6 +99,36 @@ def test_wavefront_equals_megakernel_bitwise(crt, W, H, spp, monkeypatch):
     sc.free()
 
 
+@pytest.mark.parametrize("env", [{"CRT_WF_GRAPH": "1"}, {"CRT_WF_GRAPH": "1", "CRT_WF_PARTS": "1"},
+                                 {"CRT_WF_GRAPH": "1", "CRT_WF_BLOCKED": "1", "CRT_WF_PARTS": "4"}, {"CRT_WF_GRAPH": "0", "CRT_WF_BLOCKED": "1", "CRT_WF_PARTS": "3"}])
+def test_graph_replay_and_blocked_order_bitwise(crt, env, monkeypatch):
+    """Batches of iterations replayed as CUDA graphs (captured the second time a batch signature is seen), and the
+    part-major ("temporal blocking") launch order: same bits as direct launches, frame after frame (the graphs are
+    reused by the second frame, whose kernel arguments are the same)."""
+    sc = crt.builtin_scene("cornell_blob", 48)
+    W, H = 256, 160
+    monkeypatch.setenv("CRT_WF_GRAPH", "0")
+    r = make_renderer(crt, sc, W, H, crt.MODE_WAVEFRONT, aspect=W / H)
+    want = []
+    for _ in range(2):
+        st = r.render(12, 20)
+        want.append((r.accum().copy(), r.rng_state().copy(), int(st.rays)))
+        assert st.graph_launches == 0
+    r.close()
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    r = make_renderer(crt, sc, W, H, crt.MODE_WAVEFRONT, aspect=W / H)
+    for f in range(2):
+        st = r.render(12, 20)
+        assert np.array_equal(want[f][0].view(np.uint32), r.accum().view(np.uint32))
+        assert np.array_equal(want[f][1], r.rng_state())
+        assert want[f][2] == int(st.rays)
+        if env["CRT_WF_GRAPH"] == "1":
+            assert st.graph_launches > 0 and st.kernel_launches > 100
+    r.close()
+    sc.free()
+
+
 @pytest.mark.parametrize("rounds,parts", [(1, 2), (3, 1), (2, 3)])
 def test_parked_rays_resume_bitwise(crt, rounds, parts, monkeypatch):
     """extend parks the rays that are still in flight when its queue runs out (k_wf_extend "drain") and the next
