@@ -121,7 +121,13 @@ typedef struct crt_config {
     int32_t device;        /* CUDA device ordinal                                       */
     int32_t mode;          /* CRT_MODE_*                                                */
     int32_t bvh_leaf_max;  /* 0 = default (2), 1..3                                        */
-    int32_t reserved[7];   /* must be zero                                              */
+    int32_t reference_exact; /* 1 = follow the reference where its results depend on ITS acceleration structure
+                              (see crt_scene_reference_order): equal-t ties go to the primitive the reference
+                              tests last, triangles in zero-thickness leaves of its mesh BVH are not seen.
+                              crt_set_scene then replays the reference's sequential partition on the host
+                              (~5 s per million triangles). 0 (default): larger primitive id wins a tie,
+                              every triangle is seen                                     */
+    int32_t reserved[6];   /* must be zero                                              */
 } crt_config;
 
 /* ---- per-render parameters -------------------------------------------------
@@ -177,7 +183,7 @@ typedef struct crt_stats {
     uint32_t iterations;       /* wavefront iterations (extend + shade per part) of the last crt_render               */
     uint32_t graph_launches;   /* batches of the last crt_render replayed as one CUDA graph launch (their kernels are
                                   counted in kernel_launches all the same)                                             */
-    uint32_t reserved[1];
+    uint32_t unseen_triangles; /* reference-exact mode: triangles the reference's zero-thickness leaves hide (made degenerate here) */
 } crt_stats;
 
 typedef struct crt_ctx crt_ctx;
@@ -327,6 +333,19 @@ void crt_scene_free(crt_scene* scene);
 int crt_scene_load_obj(const char* const* paths, int32_t num_paths,
                        int32_t add_reference_spheres, crt_scene** out_scene,
                        char* err_buf, size_t err_len);
+
+/* ---- reference-exact mode ---------------------------------------------------------------
+ * Host-only replay of the PARTITION made by the reference's mesh BVH builder (src/Core/Mesh.cuh:121-219),
+ * mesh by mesh (mesh_tri_offset; one mesh when NULL). Any output may be NULL; each has num_triangles entries.
+ *   out_order[k]   triangle id at position k of the reference's permuted index array
+ *   out_rank[id]   the inverse: the position of triangle id. Among hits with bit-equal t the reference keeps the
+ *                  one it tests last (Mesh.cuh:73-74,293) = the larger rank; spheres come after all meshes
+ *                  (src/CUDAKernels.h:64-73, Core/BVHNode.cuh:115-156).
+ *   out_unseen[id] 1 when the triangle sits in a leaf whose unpadded box (Mesh.cuh:258-264) has zero thickness
+ *                  along an axis: AABB::hit rejects tmax <= tmin (Core/AABB.cuh:135-136), the reference never
+ *                  tests it.
+ * crt_set_scene calls this when crt_config.reference_exact is set. */
+int crt_scene_reference_order(const crt_scene* scene, uint32_t* out_order, uint32_t* out_rank, uint8_t* out_unseen);
 
 /* ---- image output (replaces the SFML window) --------------------------
  * Writes the RGBA8 image top-down (i.e. applies the reference's flipVertically,

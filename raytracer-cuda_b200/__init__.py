@@ -48,7 +48,7 @@ class Camera(C.Structure):
 
 class Config(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("device", C.c_int32), ("mode", C.c_int32),
-                ("bvh_leaf_max", C.c_int32), ("reserved", C.c_int32 * 7)]
+                ("bvh_leaf_max", C.c_int32), ("reference_exact", C.c_int32), ("reserved", C.c_int32 * 6)]
 
 
 class RenderParams(C.Structure):
@@ -64,7 +64,7 @@ class Stats(C.Structure):
                 ("nodes_fetched", C.c_uint64), ("prims_tested", C.c_uint64), ("extend_ms", C.c_float), ("shade_ms", C.c_float),
                 ("extend_launches", C.c_uint32), ("shade_launches", C.c_uint32), ("bvh_giants", C.c_uint32),
                 ("tail_ms", C.c_float), ("begin_ms", C.c_float), ("compact_ms", C.c_float), ("host_syncs", C.c_uint32),
-                ("iterations", C.c_uint32), ("graph_launches", C.c_uint32), ("reserved", C.c_uint32 * 1)]
+                ("iterations", C.c_uint32), ("graph_launches", C.c_uint32), ("unseen_triangles", C.c_uint32)]
 
 
 class CrtError(RuntimeError):
@@ -114,6 +114,7 @@ def load_library():
         "crt_write_pfm": (C.c_int, [P, C.c_char_p]),
         "crt_checkpoint_save": (C.c_int, [P, C.c_char_p]),
         "crt_checkpoint_load": (C.c_int, [P, C.c_char_p]),
+        "crt_scene_reference_order": (C.c_int, [C.POINTER(Scene), P, P, P]),
         "crt_comm_unique_id": (C.c_int, [P, C.c_size_t]),
         "crt_comm_init": (C.c_int, [P, P, C.c_int32, C.c_int32]),
         "crt_comm_destroy": (C.c_int, [P]),
@@ -143,7 +144,7 @@ API_FUNCTIONS = ["crt_api_version", "crt_create", "crt_destroy", "crt_last_error
                  "crt_get_accum", "crt_set_accum", "crt_tonemap", "crt_get_rng_state", "crt_set_rng_state",
                  "crt_get_stats", "crt_get_stream", "crt_set_stream", "crt_scene_builtin", "crt_scene_free", "crt_scene_load_obj",
                  "crt_write_ppm", "crt_write_pfm", "crt_checkpoint_save", "crt_checkpoint_load",
-                 "crt_comm_unique_id", "crt_comm_init", "crt_comm_destroy", "crt_comm_info", "crt_reduce_accum",
+                 "crt_scene_reference_order", "crt_comm_unique_id", "crt_comm_init", "crt_comm_destroy", "crt_comm_info", "crt_reduce_accum",
                  "crt_group_create", "crt_group_destroy", "crt_group_last_error", "crt_group_size", "crt_group_ctx",
                  "crt_group_set_scene", "crt_group_set_camera", "crt_group_init_rng", "crt_group_render", "crt_group_get_stats"]
 COMM_ID_BYTES = 128
@@ -251,14 +252,15 @@ def make_scene_struct(positions, indices, tri_material, spheres, sphere_material
 class Renderer:
     """CUDARenderer-shaped wrapper of a crt_ctx (reference: src/CUDARenderer.cuh:9-29)."""
 
-    def __init__(self, width, height, device=0, mode=MODE_WAVEFRONT, bvh_leaf_max=0, borrowed_ctx=None):
+    def __init__(self, width, height, device=0, mode=MODE_WAVEFRONT, bvh_leaf_max=0, borrowed_ctx=None, reference_exact=False):
         self.lib = load_library()
         self.width, self.height = int(width), int(height)
         self._borrowed = borrowed_ctx is not None
         if self._borrowed:                      # a context owned by a DeviceGroup
             self._ctx = C.c_void_p(borrowed_ctx)
             return
-        cfg = Config(width=self.width, height=self.height, device=device, mode=mode, bvh_leaf_max=bvh_leaf_max)
+        cfg = Config(width=self.width, height=self.height, device=device, mode=mode, bvh_leaf_max=bvh_leaf_max,
+                     reference_exact=1 if reference_exact else 0)
         self._ctx = C.c_void_p()
         rc = self.lib.crt_create(C.byref(self._ctx), C.byref(cfg))
         if rc != CRT_OK:
@@ -383,6 +385,18 @@ class Renderer:
             self.close()
         except Exception:
             pass
+
+
+def reference_order(scene):
+    """crt_scene_reference_order: (order, rank, unseen) of the reference builder's partition (host only, no GPU)."""
+    lib = load_library()
+    ptr = scene.pointer() if isinstance(scene, SceneHandle) else C.pointer(scene)
+    T = ptr.contents.num_triangles
+    order, rank, unseen = np.empty(T, np.uint32), np.empty(T, np.uint32), np.empty(T, np.uint8)
+    rc = lib.crt_scene_reference_order(ptr, order.ctypes.data, rank.ctypes.data, unseen.ctypes.data)
+    if rc != CRT_OK:
+        raise CrtError(rc, "crt_scene_reference_order failed")
+    return order, rank, unseen
 
 
 def comm_unique_id():

@@ -39,7 +39,8 @@ static int fail_cuda(crt_ctx* ctx, cudaError_t e, const char* what) {
 
 static void free_scene(crt_ctx* ctx) {
     cudaFree(ctx->d_pos); cudaFree(ctx->d_idx); cudaFree(ctx->d_trimat); cudaFree(ctx->d_sph); cudaFree(ctx->d_sphmat);
-    cudaFree(ctx->d_mats); cudaFree(ctx->bvh.nodes); cudaFree(ctx->bvh.prims);
+    cudaFree(ctx->d_mats); cudaFree(ctx->bvh.nodes); cudaFree(ctx->bvh.prims); cudaFree(ctx->d_trikey); cudaFree(ctx->d_key2id);
+    ctx->d_trikey = nullptr; ctx->d_key2id = nullptr;
     ctx->d_pos = nullptr; ctx->d_idx = nullptr; ctx->d_trimat = nullptr; ctx->d_sph = nullptr; ctx->d_sphmat = nullptr;
     ctx->d_mats = nullptr; ctx->bvh = WideBvh(); ctx->scene_ready = false;
 }
@@ -49,6 +50,7 @@ static SceneView scene_view(const crt_ctx* ctx) {
     v.nodes = ctx->bvh.nodes; v.prims = ctx->bvh.prims; v.mats = ctx->d_mats;
     v.num_mats = ctx->num_mats; v.num_nodes = ctx->bvh.num_nodes; v.num_prims = ctx->bvh.num_prims;
     v.giant_base = ctx->bvh.giant_base; v.giant_count = ctx->bvh.giant_count;
+    v.key_to_id = ctx->d_key2id; v.num_tris = ctx->num_tris;
     return v;
 }
 
@@ -74,6 +76,7 @@ int crt_create(crt_ctx** out_ctx, const crt_config* cfg) {
     if (cfg->width <= 0 || cfg->height <= 0 || (long long)cfg->width * cfg->height > (1ll << 30))
         return fail(nullptr, CRT_E_INVALID, "crt_create: bad image size");
     if (cfg->mode != CRT_MODE_WAVEFRONT && cfg->mode != CRT_MODE_MEGAKERNEL && cfg->mode != CRT_MODE_AUTO) return fail(nullptr, CRT_E_INVALID, "crt_create: bad mode");
+    if (cfg->reference_exact != 0 && cfg->reference_exact != 1) return fail(nullptr, CRT_E_INVALID, "crt_create: reference_exact must be 0 or 1");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev <= 0) { (void)cudaGetLastError(); return fail(nullptr, CRT_E_NO_DEVICE, "crt_create: no CUDA device (this library has no CPU fallback)"); }
@@ -166,16 +169,44 @@ int crt_set_scene(crt_ctx* ctx, const crt_scene* sc) {
     } catch (const std::bad_alloc&) {
         return fail(ctx, CRT_E_NOMEM, "crt_set_scene: out of host memory");
     }
+    // reference-exact mode: replay the reference builder's partition on the host (crt_refexact.cpp): tie keys, and the
+    // triangles its zero-thickness leaves hide, which become degenerate (v0, v0, v0) here: same id, never hit
+    std::vector<uint32_t> order, rank, idx_seen;
+    uint32_t unseen_count = 0;
+    if (ctx->cfg.reference_exact && T) {
+        try {
+            order.resize(T); rank.resize(T);
+            std::vector<uint8_t> unseen(T);
+            const int rrc = crt_scene_reference_order(sc, order.data(), rank.data(), unseen.data());
+            if (rrc != CRT_OK) return fail(ctx, rrc, "crt_set_scene: reference-order replay failed (mesh_tri_offset must tile the triangles in order)");
+            for (uint32_t t = 0; t < T; t++) unseen_count += unseen[t];
+            if (unseen_count) {
+                idx_seen.assign(sc->indices, sc->indices + (size_t)3 * T);
+                for (uint32_t t = 0; t < T; t++) if (unseen[t]) { idx_seen[3 * (size_t)t + 1] = idx_seen[3 * (size_t)t]; idx_seen[3 * (size_t)t + 2] = idx_seen[3 * (size_t)t]; }
+            }
+        } catch (const std::bad_alloc&) {
+            return fail(ctx, CRT_E_NOMEM, "crt_set_scene: out of host memory");
+        }
+    }
+    const uint32_t* host_indices = idx_seen.empty() ? sc->indices : idx_seen.data();
     CU(cudaSetDevice(ctx->cfg.device));
     CU(cudaStreamSynchronize(ctx->stream));
     free_scene(ctx);
+    ctx->num_tris = T;
+    ctx->unseen_tris = unseen_count;
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
     if (T) {
         CU(cudaMalloc(&ctx->d_pos, (size_t)sc->num_vertices * 3 * sizeof(float)));
         CU(cudaMalloc(&ctx->d_idx, (size_t)T * 3 * sizeof(uint32_t)));
         CU(cudaMalloc(&ctx->d_trimat, (size_t)T * sizeof(int32_t)));
         CU(cudaMemcpyAsync(ctx->d_pos, sc->positions, (size_t)sc->num_vertices * 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-        CU(cudaMemcpyAsync(ctx->d_idx, sc->indices, (size_t)T * 3 * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->d_idx, host_indices, (size_t)T * 3 * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+        if (!rank.empty()) {
+            CU(cudaMalloc(&ctx->d_trikey, (size_t)T * sizeof(uint32_t)));
+            CU(cudaMalloc(&ctx->d_key2id, (size_t)T * sizeof(uint32_t)));
+            CU(cudaMemcpyAsync(ctx->d_trikey, rank.data(), (size_t)T * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+            CU(cudaMemcpyAsync(ctx->d_key2id, order.data(), (size_t)T * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+        }
         CU(cudaMemcpyAsync(ctx->d_trimat, sc->tri_material, (size_t)T * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
     }
     if (S) {
@@ -194,6 +225,7 @@ int crt_set_scene(crt_ctx* ctx, const crt_scene* sc) {
     SceneInput in;
     in.positions = ctx->d_pos; in.indices = ctx->d_idx; in.tri_material = ctx->d_trimat;
     in.spheres = ctx->d_sph; in.sphere_material = ctx->d_sphmat; in.num_triangles = T; in.num_spheres = S;
+    in.tri_key = ctx->d_trikey;
     cudaError_t ce = cudaSuccess;
     int rc = build_bvh_device(in, (uint32_t)ctx->cfg.bvh_leaf_max, ctx->stream, ctx->num_sms, ctx->bvh, &ctx->stats.bvh_build_ms, &ce);
     if (rc != CRT_OK) {
@@ -209,6 +241,7 @@ int crt_set_scene(crt_ctx* ctx, const crt_scene* sc) {
     ctx->stats.bvh_prims = ctx->bvh.num_prims;
     ctx->stats.bvh_depth = ctx->bvh.depth;
     ctx->stats.bvh_giants = ctx->bvh.giant_count;
+    ctx->stats.unseen_triangles = ctx->unseen_tris;
     ctx->scene_ready = true;
     return CRT_OK;
 }

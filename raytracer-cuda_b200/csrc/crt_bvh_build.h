@@ -46,6 +46,7 @@ struct SceneInput {   // device (or host-sim) pointers to the caller's flat arra
     const int32_t* sphere_material;
     uint32_t num_triangles;
     uint32_t num_spheres;
+    const uint32_t* tri_key = nullptr;   // optional: the tie key stored in a triangle's record instead of its id (reference-exact mode)
 };
 
 CRT_HD float fmin3(float a, float b, float c) { return fminf(a, fminf(b, c)); }
@@ -331,7 +332,7 @@ CRT_HD PrimRec make_prim_record(const SceneInput& in, uint32_t p) {
         const vec3 e1 = v_sub(v1, v0), e2 = v_sub(v2, v0);   // Mesh.cuh:277-278
         r.q0.x = v0.x; r.q0.y = v0.y; r.q0.z = v0.z; r.q0.w = e1.x;
         r.q1.x = e1.y; r.q1.y = e1.z; r.q1.z = e2.x; r.q1.w = e2.y;
-        r.q2.x = e2.z; r.q2.y = bits_f(p); r.q2.z = bits_f((uint32_t)in.tri_material[p]); r.q2.w = bits_f((uint32_t)PRIM_TRIANGLE);
+        r.q2.x = e2.z; r.q2.y = bits_f(in.tri_key ? in.tri_key[p] : p); r.q2.z = bits_f((uint32_t)in.tri_material[p]); r.q2.w = bits_f((uint32_t)PRIM_TRIANGLE);
     } else {
         const uint32_t j = p - in.num_triangles;
         const float rad = in.spheres[4 * j + 3];

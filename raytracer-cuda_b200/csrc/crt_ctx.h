@@ -23,6 +23,9 @@ struct crt_ctx {
     float* d_sph = nullptr;
     int32_t* d_sphmat = nullptr;
     crt::MatRec* d_mats = nullptr;
+    uint32_t* d_trikey = nullptr;    // reference-exact mode: tie key per triangle (its rank in the reference's order)
+    uint32_t* d_key2id = nullptr;    // and the inverse, for the primary-id buffer
+    uint32_t num_tris = 0, unseen_tris = 0;
     uint32_t num_mats = 0;
     crt::WideBvh bvh{};
     bool scene_ready = false;

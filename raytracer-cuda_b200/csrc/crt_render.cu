@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(256) k_primary(SceneView scene, Camera cam, in
     camera_ray(cam, x, y, width, height, rng, o, d);
     HitRec h;
     const bool hit = trace_closest<false>(scene, o, d, 0.001f, INFINITY, h, nullptr);
-    ids[pix] = hit ? h.id : -1;
+    ids[pix] = hit ? ((scene.key_to_id && (uint32_t)h.id < scene.num_tris) ? (int32_t)scene.key_to_id[h.id] : h.id) : -1;
     if (tout) tout[pix] = hit ? h.t : INFINITY;
 }
 

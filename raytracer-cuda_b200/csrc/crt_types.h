@@ -61,6 +61,10 @@ struct SceneView {   // device pointers
     uint32_t num_prims;
     uint32_t giant_base;    // prims[giant_base .. giant_base+giant_count) are outside the BVH: every ray tests them
     uint32_t giant_count;
+    // reference-exact mode: a triangle's record carries its tie key (position in the reference's permuted order) in the
+    // id field; key_to_id[key] is the caller's triangle id (null: key = id). Spheres: key = id = num_tris + index.
+    const uint32_t* key_to_id;
+    uint32_t num_tris;
 };
 
 struct RenderConst {

@@ -55,6 +55,7 @@ hs_scene* hs_scene_create(const crt_scene* sc, int leaf_max) {
     s->view.nodes = s->bvh.nodes; s->view.prims = s->bvh.prims; s->view.mats = s->mats.data();
     s->view.num_mats = (uint32_t)s->mats.size(); s->view.num_nodes = s->bvh.num_nodes; s->view.num_prims = s->bvh.num_prims;
     s->view.giant_base = s->bvh.giant_base; s->view.giant_count = s->bvh.giant_count;
+    s->view.key_to_id = nullptr; s->view.num_tris = sc->num_triangles;
     return s;
 }
 
