@@ -44,7 +44,8 @@ enum {
     CRT_E_NOMEM       = -4,
     CRT_E_IO          = -5,  /* file could not be read / written                         */
     CRT_E_PARSE       = -6,  /* malformed OBJ / MTL                                      */
-    CRT_E_LIMIT       = -7   /* a structural limit was exceeded (stack depth, counts)    */
+    CRT_E_LIMIT       = -7,  /* a structural limit was exceeded (stack depth, counts)    */
+    CRT_E_BUSY        = -8   /* an asynchronous render owns the context: call crt_wait   */
 };
 
 /* ---- materials: mirrors CRT::MaterialType / CRT::MaterialData ------------
@@ -138,6 +139,10 @@ enum {
                                         overwriting it (the reference always overwrites,
                                         src/CUDAKernels.h:164)                          */
     CRT_RENDER_NO_TONEMAP = 1u << 1, /* skip the RGBA8 pack (multi-GPU ranks != 0)      */
+    CRT_RENDER_ASYNC = 1u << 3,      /* crt_render returns at once; the frame is driven by a host thread of the
+                                        library. Until crt_wait(ctx) returns the frame's status, every other call
+                                        on the context fails with CRT_E_BUSY (crt_get_stats and crt_last_error
+                                        excepted)                                                              */
     CRT_RENDER_TIME_KERNELS = 1u << 2 /* bracket every kernel launch with CUDA events on the
                                         launching stream and report per-kernel-class totals in
                                         crt_stats (extend_ms / shade_ms); off by default       */
@@ -227,6 +232,9 @@ int crt_set_camera(crt_ctx* ctx, const crt_camera* cam);
  * Continues each pixel's RNG stream where the previous call left it, like the
  * reference (src/CUDAKernels.h:153,165). */
 int crt_render(crt_ctx* ctx, const crt_render_params* params);
+
+/* Joins an asynchronous render (CRT_RENDER_ASYNC) and returns its status; CRT_OK at once when none is in flight. */
+int crt_wait(crt_ctx* ctx);
 
 /* Same as crt_render but with per-ray node/primitive counters switched on (slower);
  * fills crt_stats.nodes_fetched / prims_tested. Used for the roofline bytes-per-ray. */

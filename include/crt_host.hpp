@@ -43,6 +43,7 @@ inline const char* errorName(int rc) {   // the CRT_E_* codes of crt_api.h as te
         case CRT_E_IO: return "file could not be read or written";
         case CRT_E_PARSE: return "malformed OBJ / MTL";
         case CRT_E_LIMIT: return "structural limit exceeded";
+        case CRT_E_BUSY: return "an asynchronous render owns the context (crt_wait)";
         default: return "unknown error";
     }
 }

@@ -18,10 +18,10 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("CRT_LIB") or os.path.join(_HERE, "libcrt_b200.so")   # CRT_LIB: tuning builds of the same library
 
 CRT_OK = 0
-E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_IO, E_PARSE, E_LIMIT = -1, -2, -3, -4, -5, -6, -7
+E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_IO, E_PARSE, E_LIMIT, E_BUSY = -1, -2, -3, -4, -5, -6, -7, -8
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT = 0, 1, 2, 3
 MODE_WAVEFRONT, MODE_MEGAKERNEL, MODE_AUTO = 0, 1, 2
-RENDER_ACCUMULATE, RENDER_NO_TONEMAP, RENDER_TIME_KERNELS = 1, 2, 4
+RENDER_ACCUMULATE, RENDER_NO_TONEMAP, RENDER_TIME_KERNELS, RENDER_ASYNC = 1, 2, 4, 8
 REFERENCE_SEED = 1804289383  # glibc rand() first value = what CUDARenderer::initialize passes (CUDARenderer.cuh:46)
 
 
@@ -96,6 +96,7 @@ def load_library():
         "crt_set_camera": (C.c_int, [P, C.POINTER(Camera)]),
         "crt_render": (C.c_int, [P, C.POINTER(RenderParams)]),
         "crt_render_counted": (C.c_int, [P, C.POINTER(RenderParams)]),
+        "crt_wait": (C.c_int, [P]),
         "crt_primary_ids": (C.c_int, [P, C.c_uint64, C.c_uint64, P, P]),
         "crt_get_image_rgba8": (C.c_int, [P, P, C.POINTER(P)]),
         "crt_get_accum": (C.c_int, [P, P, C.POINTER(P)]),
@@ -140,7 +141,7 @@ def load_library():
 
 
 API_FUNCTIONS = ["crt_api_version", "crt_create", "crt_destroy", "crt_last_error", "crt_init_rng", "crt_set_scene",
-                 "crt_set_camera", "crt_render", "crt_render_counted", "crt_primary_ids", "crt_get_image_rgba8",
+                 "crt_set_camera", "crt_render", "crt_render_counted", "crt_wait", "crt_primary_ids", "crt_get_image_rgba8",
                  "crt_get_accum", "crt_set_accum", "crt_tonemap", "crt_get_rng_state", "crt_set_rng_state",
                  "crt_get_stats", "crt_get_stream", "crt_set_stream", "crt_scene_builtin", "crt_scene_free", "crt_scene_load_obj",
                  "crt_write_ppm", "crt_write_pfm", "crt_checkpoint_save", "crt_checkpoint_load",
@@ -269,6 +270,8 @@ class Renderer:
             raise CrtError(rc, msg)
 
     def _check(self, rc):
+        if rc == E_BUSY:
+            raise CrtError(rc, "an asynchronous render owns the context: call wait()")
         if rc != CRT_OK:
             raise CrtError(rc, self.lib.crt_last_error(self._ctx).decode(errors="replace"))
 
@@ -290,6 +293,11 @@ class Renderer:
                          rr_max_prob=float(rr_max_prob), flags=int(flags))
         fn = self.lib.crt_render_counted if counted else self.lib.crt_render
         self._check(fn(self._ctx, C.byref(p)))
+        return None if (int(flags) & RENDER_ASYNC) else self.stats()
+
+    def wait(self):
+        """crt_wait: join a render started with RENDER_ASYNC; returns its stats."""
+        self._check(self.lib.crt_wait(self._ctx))
         return self.stats()
 
     def primary_ids(self, seed=REFERENCE_SEED, subsequence_base=0):

@@ -37,6 +37,12 @@ static int fail_cuda(crt_ctx* ctx, cudaError_t e, const char* what) {
         if (e__ != cudaSuccess) return fail_cuda(ctx, e__, #call);      \
     } while (0)
 
+// An asynchronous render (CRT_RENDER_ASYNC) owns the context until crt_wait: every other call is refused meanwhile.
+#define NOT_BUSY(ctx)                                                                                              \
+    do {                                                                                                           \
+        if ((ctx) && (ctx)->async_pending) return CRT_E_BUSY;                                                     \
+    } while (0)
+
 static void free_scene(crt_ctx* ctx) {
     cudaFree(ctx->d_pos); cudaFree(ctx->d_idx); cudaFree(ctx->d_trimat); cudaFree(ctx->d_sph); cudaFree(ctx->d_sphmat);
     cudaFree(ctx->d_mats); cudaFree(ctx->bvh.nodes); cudaFree(ctx->bvh.prims); cudaFree(ctx->d_trikey); cudaFree(ctx->d_key2id);
@@ -114,6 +120,7 @@ int crt_create(crt_ctx** out_ctx, const crt_config* cfg) {
 
 void crt_destroy(crt_ctx* ctx) {
     if (!ctx) return;
+    if (ctx->worker.joinable()) ctx->worker.join();   // an asynchronous render still in flight finishes first
     cudaSetDevice(ctx->cfg.device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     crt_comm_release_(ctx);
@@ -128,6 +135,7 @@ void crt_destroy(crt_ctx* ctx) {
 }
 
 int crt_init_rng(crt_ctx* ctx, uint64_t seed, uint64_t subsequence_base) {
+    NOT_BUSY(ctx);
     if (!ctx) return CRT_E_INVALID;
     CU(cudaSetDevice(ctx->cfg.device));
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
@@ -140,6 +148,7 @@ int crt_init_rng(crt_ctx* ctx, uint64_t seed, uint64_t subsequence_base) {
 }
 
 int crt_set_scene(crt_ctx* ctx, const crt_scene* sc) {
+    NOT_BUSY(ctx);
     if (!ctx || !sc) return ctx ? fail(ctx, CRT_E_INVALID, "crt_set_scene: null scene") : CRT_E_INVALID;
     const uint32_t T = sc->num_triangles, S = sc->num_spheres;
     if (T + S == 0) return fail(ctx, CRT_E_INVALID, "crt_set_scene: empty scene");
@@ -247,6 +256,7 @@ int crt_set_scene(crt_ctx* ctx, const crt_scene* sc) {
 }
 
 int crt_set_camera(crt_ctx* ctx, const crt_camera* cam) {
+    NOT_BUSY(ctx);
     if (!ctx || !cam) return ctx ? fail(ctx, CRT_E_INVALID, "crt_set_camera: null camera") : CRT_E_INVALID;
     ctx->cam = make_camera(*cam);
     ctx->cam_ready = true;
@@ -298,10 +308,37 @@ static int render_impl(crt_ctx* ctx, const crt_render_params* p, bool counted) {
     return CRT_OK;
 }
 
-int crt_render(crt_ctx* ctx, const crt_render_params* p) { return render_impl(ctx, p, false); }
-int crt_render_counted(crt_ctx* ctx, const crt_render_params* p) { return render_impl(ctx, p, true); }
+int crt_render(crt_ctx* ctx, const crt_render_params* p) {
+    NOT_BUSY(ctx);
+    if (ctx && p && (p->flags & CRT_RENDER_ASYNC)) {
+        // the wavefront loop needs the host (it reads queue lengths back between batches), so "asynchronous" means a
+        // host thread of the library's own drives the frame; the caller gets its thread back at once
+        if (ctx->worker.joinable()) ctx->worker.join();
+        ctx->async_params = *p;
+        ctx->async_params.flags &= ~(uint32_t)CRT_RENDER_ASYNC;
+        ctx->async_pending = true;
+        try {
+            ctx->worker = std::thread([ctx] { ctx->async_rc = render_impl(ctx, &ctx->async_params, false); });
+        } catch (...) {
+            ctx->async_pending = false;
+            return fail(ctx, CRT_E_NOMEM, "crt_render: could not start the render thread");
+        }
+        return CRT_OK;
+    }
+    return render_impl(ctx, p, false);
+}
+int crt_render_counted(crt_ctx* ctx, const crt_render_params* p) { NOT_BUSY(ctx); return render_impl(ctx, p, true); }
+
+int crt_wait(crt_ctx* ctx) {
+    if (!ctx) return CRT_E_INVALID;
+    if (!ctx->async_pending) return CRT_OK;
+    if (ctx->worker.joinable()) ctx->worker.join();
+    ctx->async_pending = false;
+    return ctx->async_rc;
+}
 
 int crt_primary_ids(crt_ctx* ctx, uint64_t seed, uint64_t subsequence_base, int32_t* out_ids, float* out_t) {
+    NOT_BUSY(ctx);
     if (!ctx || !out_ids) return ctx ? fail(ctx, CRT_E_INVALID, "crt_primary_ids: null output") : CRT_E_INVALID;
     if (!ctx->scene_ready || !ctx->cam_ready) return fail(ctx, CRT_E_INVALID, "crt_primary_ids: scene and camera must be set");
     CU(cudaSetDevice(ctx->cfg.device));
@@ -321,6 +358,7 @@ int crt_primary_ids(crt_ctx* ctx, uint64_t seed, uint64_t subsequence_base, int3
 }
 
 int crt_get_image_rgba8(crt_ctx* ctx, void* host, void** out_dev) {
+    NOT_BUSY(ctx);
     if (!ctx) return CRT_E_INVALID;
     CU(cudaSetDevice(ctx->cfg.device));
     if (out_dev) *out_dev = ctx->fb.rgba8;
@@ -332,6 +370,7 @@ int crt_get_image_rgba8(crt_ctx* ctx, void* host, void** out_dev) {
 }
 
 int crt_get_accum(crt_ctx* ctx, float* host, void** out_dev) {
+    NOT_BUSY(ctx);
     if (!ctx) return CRT_E_INVALID;
     CU(cudaSetDevice(ctx->cfg.device));
     if (out_dev) *out_dev = ctx->fb.accum;
@@ -343,6 +382,7 @@ int crt_get_accum(crt_ctx* ctx, float* host, void** out_dev) {
 }
 
 int crt_set_accum(crt_ctx* ctx, const float* host) {
+    NOT_BUSY(ctx);
     if (!ctx || !host) return ctx ? fail(ctx, CRT_E_INVALID, "crt_set_accum: null buffer") : CRT_E_INVALID;
     CU(cudaSetDevice(ctx->cfg.device));
     CU(cudaMemcpyAsync(ctx->fb.accum, host, (size_t)ctx->cfg.width * ctx->cfg.height * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
@@ -351,6 +391,7 @@ int crt_set_accum(crt_ctx* ctx, const float* host) {
 }
 
 int crt_tonemap(crt_ctx* ctx) {
+    NOT_BUSY(ctx);
     if (!ctx) return CRT_E_INVALID;
     CU(cudaSetDevice(ctx->cfg.device));
     CU(launch_tonemap(ctx->fb, ctx->cfg.width, ctx->cfg.height, ctx->stream));
@@ -359,6 +400,7 @@ int crt_tonemap(crt_ctx* ctx) {
 }
 
 int crt_get_rng_state(crt_ctx* ctx, uint32_t* host, void** out_dev) {
+    NOT_BUSY(ctx);
     if (!ctx) return CRT_E_INVALID;
     CU(cudaSetDevice(ctx->cfg.device));
     if (out_dev) *out_dev = ctx->fb.rng;
@@ -370,6 +412,7 @@ int crt_get_rng_state(crt_ctx* ctx, uint32_t* host, void** out_dev) {
 }
 
 int crt_set_rng_state(crt_ctx* ctx, const uint32_t* host) {
+    NOT_BUSY(ctx);
     if (!ctx || !host) return ctx ? fail(ctx, CRT_E_INVALID, "crt_set_rng_state: null buffer") : CRT_E_INVALID;
     CU(cudaSetDevice(ctx->cfg.device));
     CU(cudaMemcpyAsync(ctx->fb.rng, host, (size_t)ctx->cfg.width * ctx->cfg.height * 6 * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
@@ -385,6 +428,7 @@ int crt_get_stats(crt_ctx* ctx, crt_stats* out) {
 }
 
 int crt_set_stream(crt_ctx* ctx, void* stream) {
+    NOT_BUSY(ctx);
     if (!ctx) return CRT_E_INVALID;
     CU(cudaSetDevice(ctx->cfg.device));
     CU(cudaStreamSynchronize(ctx->stream));

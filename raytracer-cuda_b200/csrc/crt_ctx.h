@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <string>
+#include <thread>
 
 #include "../../include/crt_api.h"
 #include "crt_internal.h"
@@ -33,6 +34,11 @@ struct crt_ctx {
     bool cam_ready = false;
     crt::WavefrontState* wf = nullptr;
     crt_stats stats{};
+    // CRT_RENDER_ASYNC: the frame loop (which reads queue lengths back) runs on this host thread until crt_wait
+    std::thread worker;
+    bool async_pending = false;
+    int async_rc = 0;
+    crt_render_params async_params{};
     void* comm = nullptr;            // ncclComm_t of crt_comm_init (crt_comm.cu); null = single GPU
     int comm_rank = 0, comm_nranks = 1;
     std::string err;

@@ -117,6 +117,7 @@ def test_graph_replay_and_blocked_order_bitwise(crt, env, monkeypatch):
     r.close()
     for k, v in env.items():
         monkeypatch.setenv(k, v)
+    monkeypatch.setenv("CRT_TAIL_LIVE", "0")     # batches with a part in its tail stages are launched directly: keep this small frame out of the tail
     r = make_renderer(crt, sc, W, H, crt.MODE_WAVEFRONT, aspect=W / H)
     for f in range(2):
         st = r.render(12, 20)
@@ -413,6 +414,14 @@ def test_empty_and_ragged_scenes(crt):
     s, keep = crt.make_scene_struct([[0, 0, 0], [1, 0, 0], [0, 1, 0]], [[0, 1, 7]], [0], np.zeros((0, 4)), [], mats)
     with pytest.raises(crt.CrtError):
         r.set_scene(s)                            # vertex index out of range
+    # a negative or NaN albedo is refused (the wavefront kernels keep a flag in the sign bit of throughput.x); -0.0 is accepted
+    for bad in ((-0.1, 0.5, 0.5), (0.5, float("nan"), 0.5), (0.5, 0.5, float("inf"))):
+        s, keep = crt.make_scene_struct(np.zeros((0, 3)), np.zeros((0, 3)), [], [[0, 0, -3, 1]], [0], [(crt.MAT_LAMBERTIAN, bad, (0, 0, 0), 0.0, 1.0)])
+        with pytest.raises(crt.CrtError) as e:
+            r.set_scene(s)
+        assert e.value.code == crt.E_INVALID and "albedo" in str(e.value)
+    s, keep = crt.make_scene_struct(np.zeros((0, 3)), np.zeros((0, 3)), [], [[0, 0, -3, 1]], [0], [(crt.MAT_METAL, (-0.0, 0.5, 0.5), (0, 0, 0), 0.0, 1.0)])
+    r.set_scene(s)
     # one sphere only, material index out of range: the reference neither scatters nor terminates
     # (CUDAKernels.h:127,135); the path burns its bounces and returns black
     s, keep = crt.make_scene_struct(np.zeros((0, 3)), np.zeros((0, 3)), [], [[0, 0, -3, 1]], [5], mats)
@@ -574,4 +583,35 @@ def test_obj_scene_matches_oracle(crt, tmp_path, mode):
     assert rad.max() > 1.0                   # the lamp is seen directly
     r.close()
     osc.close()
+    sc.free()
+
+
+def test_async_render_and_wait(crt):
+    """CRT_RENDER_ASYNC: crt_render returns at once, the frame runs on a host thread of the library; the
+    context refuses other calls with CRT_E_BUSY until crt_wait, after which the frame is the synchronous one bit for bit."""
+    sc = crt.builtin_scene("cornell_blob", 48)
+    W, H = 640, 360
+    r = make_renderer(crt, sc, W, H, crt.MODE_WAVEFRONT)
+    st = r.render(16, 20)
+    want = (r.accum().copy(), r.rng_state().copy(), int(st.rays))
+    r.initialize(SEED, 0)
+    assert r.render(16, 20, flags=crt.RENDER_ASYNC) is None
+    with pytest.raises(crt.CrtError) as e:
+        r.accum()
+    assert e.value.code == crt.E_BUSY
+    with pytest.raises(crt.CrtError):
+        r.render(1, 8)
+    st = r.wait()
+    assert int(st.rays) == want[2]
+    assert np.array_equal(r.accum().view(np.uint32), want[0].view(np.uint32))
+    assert np.array_equal(r.rng_state(), want[1])
+    assert r.wait().rays == st.rays          # nothing in flight: returns at once
+    # a failing asynchronous render reports through crt_wait
+    r2 = crt.Renderer(32, 32)
+    r2.render(1, 8, flags=crt.RENDER_ASYNC)
+    with pytest.raises(crt.CrtError) as e:
+        r2.wait()
+    assert e.value.code == crt.E_INVALID
+    r2.close()
+    r.close()
     sc.free()
