@@ -7,6 +7,10 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+
 #include "crt_bvh_driver.h"
 #include "crt_internal.h"
 
@@ -26,13 +30,23 @@ struct CudaExec {
 
     void note(cudaError_t e) { if (err == cudaSuccess && e != cudaSuccess) err = e; }
 
+    double alloc_host_ms = 0.0, free_host_ms = 0.0;   // host time spent inside cudaMalloc / cudaFree (CRT_BUILD_TRACE)
+    size_t alloc_bytes = 0;
     template <class T> T* alloc(size_t n) {
         void* p = nullptr;
+        const auto t0 = std::chrono::steady_clock::now();
         cudaError_t e = cudaMalloc(&p, (n ? n : 1) * sizeof(T));
+        alloc_host_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        alloc_bytes += (n ? n : 1) * sizeof(T);
         if (e != cudaSuccess) { note(e); return nullptr; }
         return (T*)p;
     }
-    void release(void* p) { if (p) note(cudaFree(p)); }
+    void release(void* p) {
+        if (!p) return;
+        const auto t0 = std::chrono::steady_clock::now();
+        note(cudaFree(p));
+        free_host_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
 
     template <class F> void for_n(int n, const F& f) {
         if (n <= 0) return;
@@ -68,6 +82,11 @@ struct CudaExec {
         if (cub_tmp) note(cub::DeviceScan::ExclusiveSum(cub_tmp, bytes, in, out, n, stream));
     }
 
+    void fill_u32(uint32_t* p, uint32_t v, size_t n) {
+        if (v == 0u) note(cudaMemsetAsync(p, 0, n * sizeof(uint32_t), stream));
+        else note(cudaErrorInvalidValue);   // only zero fills are needed
+    }
+
     void upload(void* d, const void* s, size_t b) {
         note(cudaMemcpyAsync(d, s, b, cudaMemcpyHostToDevice, stream));
         note(cudaStreamSynchronize(stream));   // the source is usually a stack temporary
@@ -95,6 +114,9 @@ int build_bvh_device(const SceneInput& dev_in, uint32_t leaf_max, cudaStream_t s
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     if (ex.cub_tmp) cudaFree(ex.cub_tmp);
+    if (getenv("CRT_BUILD_TRACE"))
+        fprintf(stderr, "bvh_build_trace: %.2f ms between the stream events; host time inside cudaMalloc %.2f ms (%zu MB in temporaries + outputs), inside cudaFree %.2f ms\n",
+                ms, ex.alloc_host_ms, ex.alloc_bytes >> 20, ex.free_host_ms);
     if (build_ms) *build_ms = ms;
     if (cuda_err) *cuda_err = ex.err;
     if (ex.err != cudaSuccess) return CRT_E_CUDA;

@@ -14,9 +14,11 @@
 //   2. 63-bit Morton codes of the centroids, radix sort       (MortonFn, Exec::sort_pairs)
 //   3. PLOC (Meister & Bittner 2018): repeat { nearest neighbour within +-R along the Morton
 //      order by surface area of the union; merge mutual pairs; compact } until one cluster
-//   4. collapse to 8-wide nodes level by level: greedy largest-area expansion, leaves of <=
-//      leaf_max primitives, octant-ordered child slots, 8-bit quantised child boxes
-//      (Ylitie, Karras, Laine 2017), primitive records written in leaf order.
+//   4. collapse to 8-wide nodes: a bottom-up dynamic programme over the binary tree chooses, for every binary node
+//      and every j = 1..7, the cheapest way to cover its subtree with at most j children of a wide node
+//      (CollapseCostFn; Ylitie, Karras, Laine 2017, section 3.1), then the wide nodes are emitted level by level
+//      following those decisions (CollapseFn): leaves of <= leaf_max primitives, octant-ordered child slots,
+//      8-bit quantised child boxes, primitive records written in leaf order.
 #pragma once
 #include "crt_types.h"
 
@@ -32,6 +34,14 @@ CRT_HD uint32_t atomic_add_u32(uint32_t* p, uint32_t v) { uint32_t o = *p; *p = 
 CRT_HD void atomic_min_i32(int32_t* p, int32_t v) { if (v < *p) *p = v; }
 CRT_HD void atomic_max_i32(int32_t* p, int32_t v) { if (v > *p) *p = v; }
 CRT_HD void atomic_max_u64(unsigned long long* p, unsigned long long v) { if (v > *p) *p = v; }
+#endif
+
+#if defined(__CUDA_ARCH__)
+CRT_HD void thread_fence() { __threadfence(); }
+CRT_HD float load_cg(const float* p) { return __ldcg(p); }   // past L1: written by a thread of another SM
+#else
+CRT_HD void thread_fence() {}
+CRT_HD float load_cg(const float* p) { return *p; }
 #endif
 
 // order-preserving float <-> int32 (for atomic min/max on floats)
@@ -345,6 +355,88 @@ CRT_HD PrimRec make_prim_record(const SceneInput& in, uint32_t p) {
 
 CRT_HD void GiantRecordsFn::operator()(int k) const { prims[base + (uint32_t)k] = make_prim_record(in, giants.id[k]); }
 
+// ---- collapse, step 1: which binary subtrees become the children of which wide node ----------------------------
+// cost(n, 1) = min( leaf: area * prims * C_PRIM   (only if the subtree holds <= leaf_max primitives),
+//                   wide node rooted at n: min_i cost(left, i) + cost(right, 8 - i) + area * C_NODE )
+// cost(n, j) = min( cost(n, j - 1), min_k cost(left, k) + cost(right, j - k) )        j = 2..7
+// (area = half surface area of the subtree's box: the SAH's hit probability up to a constant). The greedy "open the
+// largest child until there are 8" rule that this replaces left the wide nodes half empty (3.9 of 8 slots used on
+// the benchmark scenes: subtrees of 3-5 primitives at the bottom of a PLOC tree each became a node of their own).
+// C_PRIM / C_NODE = 0.7: measured issue cost of a primitive test (60 instructions at ~9 active lanes) against a node
+// visit (250 instructions at ~27 lanes) in k_wf_extend.
+#define CRT_COST_NODE 1.0f
+#define CRT_COST_PRIM 0.7f
+
+struct ParentFn {   // over the inner binary nodes [first_inner, first_inner + n)
+    const f4* blo;
+    const f4* bhi;
+    uint32_t* parent;
+    uint32_t first_inner;
+    CRT_HD void operator()(int k) const {
+        const uint32_t b = first_inner + (uint32_t)k;
+        parent[f_bits(blo[b].w)] = b;
+        parent[f_bits(bhi[b].w)] = b;
+    }
+};
+
+struct CollapseCostFn {   // over the leaves; a thread climbs while it is the second child to arrive at a node
+    const f4* blo;
+    const f4* bhi;
+    const uint32_t* bcount;
+    const uint32_t* parent;
+    uint32_t* arrived;     // zero-filled
+    float* cost;           // [node * 8 + j], j = 1..7
+    uint8_t* dec;          // [node * 8 + j]: j = 1: 0 = leaf, i = wide node with i children from the left subtree;
+                           //                  j > 1: 0 = as cost(n, j - 1), k = k children from the left, j - k from the right
+    uint32_t leaf_max;
+    uint32_t root;
+
+    CRT_HD void operator()(int i) const {
+        uint32_t n = (uint32_t)i;
+        {
+            const float a = box_half_area(blo[n], bhi[n]) * CRT_COST_PRIM;
+            for (int j = 1; j < 8; j++) { cost[(size_t)n * 8 + j] = a; dec[(size_t)n * 8 + j] = 0; }
+        }
+        while (n != root) {
+            const uint32_t p = parent[n];
+            thread_fence();
+            if (atomic_add_u32(&arrived[p], 1u) == 0u) return;   // the sibling's thread goes on from here
+            thread_fence();
+            const uint32_t l = f_bits(blo[p].w), r = f_bits(bhi[p].w);
+            float cl[8], cr[8];
+            for (int j = 1; j < 8; j++) { cl[j] = load_cg(&cost[(size_t)l * 8 + j]); cr[j] = load_cg(&cost[(size_t)r * 8 + j]); }
+            const float area = box_half_area(blo[p], bhi[p]);
+            float best = INFINITY;
+            int best_i = 1;
+            for (int k = 1; k < 8; k++) {
+                const float v = cl[k] + cr[8 - k];
+                if (v < best) { best = v; best_i = k; }
+            }
+            best += area * CRT_COST_NODE;
+            float c[8];
+            c[1] = best;
+            uint8_t d1 = (uint8_t)best_i;
+            if (bcount[p] <= leaf_max) {
+                const float leaf = area * (float)bcount[p] * CRT_COST_PRIM;
+                if (leaf <= best) { c[1] = leaf; d1 = 0; }
+            }
+            dec[(size_t)p * 8 + 1] = d1;
+            for (int j = 2; j < 8; j++) {
+                float b = c[j - 1];
+                uint8_t d = 0;
+                for (int k = 1; k < j; k++) {
+                    const float v = cl[k] + cr[j - k];
+                    if (v < b) { b = v; d = (uint8_t)k; }
+                }
+                c[j] = b;
+                dec[(size_t)p * 8 + j] = d;
+            }
+            for (int j = 1; j < 8; j++) cost[(size_t)p * 8 + j] = c[j];
+            n = p;
+        }
+    }
+};
+
 struct CollapseFn {
     const f4* blo;
     const f4* bhi;
@@ -356,6 +448,7 @@ struct CollapseFn {
     uint32_t* counters;      // [0] wide nodes allocated, [1] primitive records allocated
     uint32_t level_begin;
     uint32_t leaf_max;       // <= 3
+    const uint8_t* dec;      // CollapseCostFn's decisions
 
     CRT_HD uint32_t left_of(uint32_t b) const { return f_bits(blo[b].w); }
     CRT_HD uint32_t right_of(uint32_t b) const { return f_bits(bhi[b].w); }
@@ -379,22 +472,31 @@ struct CollapseFn {
             ch[0] = b;
             nch = 1;
         } else {
-            ch[0] = left_of(b);
-            ch[1] = right_of(b);
-            nch = 2;
-            while (nch < 8) {                 // open the largest inner child until 8 children
-                int best = -1;
-                float best_area = -1.f;
-                for (int i = 0; i < nch; i++) {
-                    if (bcount[ch[i]] <= leaf_max) continue;
-                    if (box_max_extent(blo[ch[i]], bhi[ch[i]]) < open_min) continue;
-                    const float a = box_half_area(blo[ch[i]], bhi[ch[i]]);
-                    if (a > best_area) { best_area = a; best = i; }
+            // follow the dynamic programme: this node takes d children from its left subtree and 8 - d from its right;
+            // a subtree asked for j > 1 children is split again as the programme decided for (subtree, j)
+            uint32_t pend_n[8];
+            int pend_j[8], np = 0;
+            nch = 0;
+            {
+                const int d = (int)dec[(size_t)b * 8 + 1];
+                const int dl = d >= 1 && d <= 7 ? d : 4;
+                pend_n[np] = right_of(b); pend_j[np++] = 8 - dl;
+                pend_n[np] = left_of(b); pend_j[np++] = dl;
+            }
+            while (np > 0) {
+                const uint32_t n = pend_n[--np];
+                int j = pend_j[np];
+                int d = 0;
+                // binary leaves, subtrees the programme keeps whole, and subtrees that are tiny next to this frame
+                // (they get a frame of their own, see above) are children as they are
+                if (left_of(n) != 0xffffffffu && box_max_extent(blo[n], bhi[n]) >= open_min) {
+                    while (j > 1 && (d = (int)dec[(size_t)n * 8 + j]) == 0) j--;
+                } else {
+                    j = 1;
                 }
-                if (best < 0) break;
-                const uint32_t c = ch[best];
-                ch[best] = left_of(c);
-                ch[nch++] = right_of(c);
+                if (j <= 1) { ch[nch++] = n; continue; }
+                pend_n[np] = right_of(n); pend_j[np++] = j - d;
+                pend_n[np] = left_of(n); pend_j[np++] = d;
             }
         }
         // leaf slot or inner child?

@@ -191,11 +191,27 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
     uint32_t* wide_bnode = tmp.template alloc<uint32_t>(node_cap);
     if (!out.nodes || !out.prims || !wide_bnode) return fail_out(CRT_E_NOMEM);
     ex.upload(wide_bnode, &root, sizeof(uint32_t));
+    // 4a. the collapse's dynamic programme, bottom-up over the binary tree (leaves 0..N-1, inner nodes N..2N-2)
+    uint32_t* parent = tmp.template alloc<uint32_t>(nb);
+    uint32_t* arrived = tmp.template alloc<uint32_t>(nb);
+    float* ccost = tmp.template alloc<float>(nb * 8);
+    uint8_t* cdec = tmp.template alloc<uint8_t>(nb * 8);
+    if (!parent || !arrived || !ccost || !cdec) return fail_out(CRT_E_NOMEM);
+    ex.fill_u32(arrived, 0u, nb);
+    {
+        ParentFn fp;
+        fp.blo = blo; fp.bhi = bhi; fp.parent = parent; fp.first_inner = N;
+        ex.for_n((int)N - 1, fp);
+        CollapseCostFn fc;
+        fc.blo = blo; fc.bhi = bhi; fc.bcount = bcount; fc.parent = parent; fc.arrived = arrived; fc.cost = ccost; fc.dec = cdec;
+        fc.leaf_max = leaf_max; fc.root = root;
+        ex.for_n(n0, fc);
+    }
     uint32_t begin = 0, end = 1, depth = 0;
     while (begin < end) {
         CollapseFn f;
         f.blo = blo; f.bhi = bhi; f.bcount = bcount; f.in = in; f.nodes = out.nodes; f.prims = out.prims;
-        f.wide_bnode = wide_bnode; f.counters = counters; f.level_begin = begin; f.leaf_max = leaf_max;
+        f.wide_bnode = wide_bnode; f.counters = counters; f.level_begin = begin; f.leaf_max = leaf_max; f.dec = cdec;
         ex.for_n((int)(end - begin), f);
         uint32_t c[2];
         ex.download(c, counters, sizeof(c));

@@ -22,6 +22,8 @@
 #include <cstring>
 #include <vector>
 
+#include <cub/device/device_radix_sort.cuh>
+
 #include "crt_internal.h"
 #include "crt_shade.h"
 
@@ -50,6 +52,11 @@ struct WfPart {
     int tail = 0;                   // 0 = wavefront iterations, 1 = handed to k_wf_tail (closing extend still to run), 2 = tail stages
     cudaStream_t stream = nullptr;  // part 0 runs on the caller's stream
     cudaEvent_t ev_done = nullptr;
+    // CRT_EXTEND_OCTANT experiment: a copy of the queue sorted by ray-direction octant, read by extend only
+    uint32_t* oct_keys[2] = {nullptr, nullptr};
+    uint32_t* oct_vals[2] = {nullptr, nullptr};
+    void* oct_tmp = nullptr;
+    size_t oct_tmp_bytes = 0;
 };
 
 // One batch of iterations (16 x parts x (extend, shade) + the compaction triples + the queue-length read-backs) as an
@@ -63,6 +70,7 @@ struct WfGraph {
 struct WavefrontState {
     std::vector<WfGraph> graphs;
     int use_graph = 1;               // env CRT_WF_GRAPH: replay a batch whose launches were seen before as one CUDA graph launch
+    int extend_octant = 0;           // env CRT_EXTEND_OCTANT: bracket experiment, extend reads a copy of the queue sorted by direction octant (cub radix sort per iteration)
     int blocked = 0;                 // env CRT_WF_BLOCKED: temporal blocking experiment, a part runs its whole batch before the next part starts (one stream)
     float4* A = nullptr;
     float4* B = nullptr;
@@ -209,6 +217,21 @@ __global__ void __launch_bounds__(256) k_compact_scatter(const uint32_t* queue_i
     }
 }
 
+// ---- CRT_EXTEND_OCTANT (experiment): sort key = direction octant of the queued ray, 8 = finished entry ----------
+__global__ void __launch_bounds__(256) k_octant_keys(const uint32_t* queue, const uint32_t* qcount, int cur, const float4* B, uint32_t* keys, uint32_t* vals, uint32_t n) {
+    const uint32_t count = qcount[cur];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t pix = i < count ? queue[i] : QUEUE_DEAD;
+        uint32_t key = 8u;
+        if (pix != QUEUE_DEAD) {
+            const float4 b = B[pix];
+            key = (b.x < 0.f ? 4u : 0u) | (b.y < 0.f ? 2u : 0u) | (b.z < 0.f ? 1u : 0u);
+        }
+        keys[i] = key;
+        vals[i] = pix;
+    }
+}
+
 // ---- begin: first camera ray of every pixel, queue = all pixels ---------------------------------
 struct BeginQueues {
     uint32_t* queue[CRT_WF_MAX_PARTS];
@@ -259,6 +282,9 @@ struct WarpPool {
 
 #ifndef CRT_EXTEND_THREADS
 #define CRT_EXTEND_THREADS 256
+#endif
+#ifndef CRT_PREFETCH_NEXT
+#define CRT_PREFETCH_NEXT 0   // 1: L2 prefetch of the node on top of the traversal stack during every node visit (experiment)
 #endif
 #ifndef CRT_SMEM_STACK
 #define CRT_SMEM_STACK 4   // entries of the traversal stack kept in shared memory (0 = all in local memory); see DESIGN.md 3.2
@@ -407,6 +433,17 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
             uint32_t rest = ng_y;
             const uint32_t rel = next_child(rest, octinv);
             if (rest & 0xff000000u) { st_set(sp, base, rest); sp++; }
+#if CRT_PREFETCH_NEXT
+            // experiment ("two node visits in flight"): the node this lane visits next unless the current
+            // visit finds children of its own -- the first hit child of the group on top of the stack -- is requested
+            // into L2 while the current visit computes
+            if (sp > 0) {
+                const uint2 top = st_get(sp - 1);
+                uint32_t tr = top.y;
+                const uint32_t r2 = next_child(tr, octinv);
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(scene.nodes + (top.x + r2)));
+            }
+#endif
             if (COUNT) c_nodes++;
             const float tmax = COOP ? __uint_as_float((uint32_t)(S.best[lane] >> 32)) : rec.t;
             visit_node(scene.nodes + (base + rel), o, idx, idy, idz, tmin, tmax, octinv, ng_x, ng_y, tg_x, tg_y, magic);
@@ -888,6 +925,7 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
     if (const char* v = getenv("CRT_SHADE_BULK")) s->shade_bulk = atoi(v);
     if (const char* v = getenv("CRT_WF_GRAPH")) s->use_graph = atoi(v);
     if (const char* v = getenv("CRT_WF_BLOCKED")) s->blocked = atoi(v);
+    if (const char* v = getenv("CRT_EXTEND_OCTANT")) s->extend_octant = atoi(v);
     if (e == cudaSuccess) e = s->shade_bulk ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade_bulk, 256, 0)
                                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade, 256, 0);
     if (const char* v = getenv("CRT_FETCH_LANES")) s->fetch_lanes = atoi(v);
@@ -918,6 +956,7 @@ void wavefront_destroy(WavefrontState* s) {
     for (WfPart& q : s->part) {
         cudaFree(q.queue[0]); cudaFree(q.queue[1]); cudaFree(q.qcount); cudaFree(q.tile_count);
         cudaFree(q.suspended[0]); cudaFree(q.suspended[1]);
+        cudaFree(q.oct_keys[0]); cudaFree(q.oct_keys[1]); cudaFree(q.oct_vals[0]); cudaFree(q.oct_vals[1]); cudaFree(q.oct_tmp);
         if (q.h_qcount) cudaFreeHost(q.h_qcount);
         if (q.ev_done) cudaEventDestroy(q.ev_done);
     }
@@ -996,7 +1035,7 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
         // these repeat from batch to batch, so the batch is captured once (the second time its signature is seen:
         // a frame whose camera moves every frame never pays for an instantiation) and replayed with ONE launch:
         // 70 launches + 2 stream joins become one cudaGraphLaunch and one synchronisation.
-        bool graphable = ws->use_graph && !timed && !counted && !ws->coop;
+        bool graphable = ws->use_graph && !timed && !counted && !ws->coop && !ws->extend_octant;
         for (int p = 0; p < parts; p++) if (!ws->part[p].done && ws->part[p].tail) graphable = false;   // tail grids follow the queue length
         WfGraph* graph = nullptr;
         bool capture = false;
@@ -1074,10 +1113,22 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                 const int par = (int)(q.extend_launches++ & 1u);
                 nl += 2;
                 if (!emit) continue;
+                uint32_t* equeue = q.queue[q.cur];
+                if (ws->extend_octant && q.live > 0u) {   // untimed by the extend events: its cost is reported by the frame time only
+                    size_t need = 0;
+                    cub::DeviceRadixSort::SortPairs(nullptr, need, q.oct_keys[0], q.oct_keys[1], q.oct_vals[0], q.oct_vals[1], (int)q.live, 0, 4, st);
+                    if (!q.oct_keys[0]) {
+                        for (int k2 = 0; k2 < 2; k2++) { cudaMalloc(&q.oct_keys[k2], (size_t)q.cap * 4); cudaMalloc(&q.oct_vals[k2], (size_t)q.cap * 4); }
+                    }
+                    if (need > q.oct_tmp_bytes) { cudaFree(q.oct_tmp); cudaMalloc(&q.oct_tmp, need); q.oct_tmp_bytes = need; }
+                    k_octant_keys<<<grid_s, 256, 0, st>>>(q.queue[q.cur], q.qcount, q.cur, w.B, q.oct_keys[0], q.oct_vals[0], q.live);
+                    cub::DeviceRadixSort::SortPairs(q.oct_tmp, need, q.oct_keys[0], q.oct_keys[1], q.oct_vals[0], q.oct_vals[1], (int)q.live, 0, 4, st);
+                    equeue = q.oct_vals[1];
+                }
                 if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p)], st);
-                if (counted) k_wf_extend<true, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
-                else if (ws->coop) k_wf_extend<false, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
-                else k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
+                if (counted) k_wf_extend<true, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, equeue, q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
+                else if (ws->coop) k_wf_extend<false, true><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, equeue, q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
+                else k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, equeue, q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, drain, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
                 if (timed) cudaEventRecord(ws->ev[3 * (b * parts + p) + 1], st);
                 if (ws->shade_bulk) k_wf_shade_bulk<<<shade_grid, 256, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur, par);
                 else k_wf_shade<<<shade_grid, 256, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur, par);

@@ -111,8 +111,11 @@ if os.path.exists(cubin):
                           capture_output=True, text=True).stdout.splitlines()
     ins = [l for l in sass if re.match(r"\s+/\*[0-9a-f]{4}\*/", l)]
     prmt = [i for i, l in enumerate(ins) if " PRMT " in l]
+    if prmt:   # the window of 330 instructions that holds the most byte decodes = one node visit
+        best = max(prmt, key=lambda i0: sum(1 for i in prmt if i0 <= i < i0 + 330))
+        prmt = [i for i in prmt if best <= i < best + 330]
     if prmt:
-        lo, hi = max(prmt[0] - 60, 0), min(prmt[-1] + 40, len(ins))
+        lo, hi = max(prmt[0] - 45, 0), min(prmt[-1] + 30, len(ins))
         with open(os.path.join(P, out + "_extend_node_visit.sass"), "w") as f:
             f.write("// cuobjdump -sass of k_wf_extend<false,false> (sm_100a), the node visit: five 16-byte node loads, per-axis set-up, 8 children x\n"
                     "// (6 PRMT byte->float, 6 FFMA, FMNMX3+FMNMX per bound, 1 compare, hit-mask insert). %d instructions between the first and the last PRMT.\n"

@@ -31,6 +31,7 @@ struct HostExec {
         *vs = vals_tmp;
     }
     void exclusive_scan(const uint32_t* in, uint32_t* out, int n) { uint32_t s = 0; for (int i = 0; i < n; i++) { out[i] = s; s += in[i]; } }
+    void fill_u32(uint32_t* p, uint32_t v, size_t n) { for (size_t i = 0; i < n; i++) p[i] = v; }
     void upload(void* d, const void* s, size_t b) { memcpy(d, s, b); }
     void download(void* d, const void* s, size_t b) { memcpy(d, s, b); }
 };
