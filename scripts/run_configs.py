@@ -7,6 +7,7 @@ sys.path.insert(0, ROOT)
 crt = importlib.import_module("raytracer-cuda_b200")
 SEED = crt.REFERENCE_SEED
 quick = "--quick" in sys.argv
+ours_only = "--ours-only" in sys.argv   # the reference kernel's numbers of BASELINE.md section 5 are not re-measured
 
 def ours(name, scene, param, W, H, spp, bounces, mode, frames=2, warm=1, aspect=None):
     sc = crt.builtin_scene(scene, param)
@@ -30,6 +31,7 @@ def ours(name, scene, param, W, H, spp, bounces, mode, frames=2, warm=1, aspect=
     r.close(); sc.free()
 
 def ref(name, scene, param, W, H, spp, bounces, frames=2, warm=1, timeout=900):
+    if ours_only: return
     exe = os.path.join(ROOT, "oracle", "_ref", "ref_render_b%d" % (8 if bounces == 8 else 20))
     cmd = [exe, "--scene", scene, "--param", str(param), "--width", str(W), "--height", str(H), "--spp", str(spp),
            "--frames", str(frames), "--warmup", str(warm), "--seed", str(SEED), "--twin"]

@@ -138,3 +138,34 @@ def test_cli_progressive_frames(cli):
     assert out.returncode == 0, out.stderr
     info = json.loads(out.stdout.strip().split("\n")[-1])
     assert info["frames"] == 6 and info["rays"] >= 6 * 128 * 72
+
+
+@pytest.mark.gpu
+def test_cli_two_gpus_equals_device_group(cli, crt, tmp_path):
+    """crt_cli --gpus 2 (CRT::CUDARendererGroup -> crt_group_*): the frame file equals the one the ctypes DeviceGroup
+    writes from GPU 0 after the same sharded render, with the peer-memory kernel and with ncclReduce."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    W, H = 160, 96
+    sc = crt.builtin_scene("cornell")
+    cam = sc.camera
+    cam.aspect = W / H
+    g = crt.DeviceGroup(W, H, [0, 1], mode=crt.MODE_WAVEFRONT)
+    g.set_scene(sc)
+    g.update_camera(cam)
+    g.initialize(SEED)
+    st = g.render(9, 8)
+    ppm_p = tmp_path / "p.ppm"
+    g.renderer(0).write_ppm(str(ppm_p))
+    g.close()
+    sc.free()
+    for extra in ([], ["--nccl"]):
+        ppm_c = tmp_path / ("c%d.ppm" % len(extra))
+        out = subprocess.run([cli, "--scene", "cornell", "--width", str(W), "--height", str(H), "--spp", "9", "--bounces", "8", "--mode", "wavefront",
+                              "--gpus", "2", "--ppm", str(ppm_c)] + extra, capture_output=True, text=True)
+        assert out.returncode == 0, out.stderr
+        info = json.loads(out.stdout.strip().split("\n")[-1])
+        assert info["gpus"] == 2 and info["rays"] == int(st.rays)
+        assert info["reduce"] == ("ncclReduce" if extra else "peer-memory kernel")
+        assert open(ppm_c, "rb").read() == open(ppm_p, "rb").read()
