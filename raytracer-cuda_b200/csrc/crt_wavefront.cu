@@ -69,6 +69,7 @@ struct WfGraph {
 
 struct WavefrontState {
     std::vector<WfGraph> graphs;
+    int batch = 16;                  // env CRT_WF_BATCH (1..16): iterations between two queue compactions / queue-length read-backs
     int use_graph = 1;               // env CRT_WF_GRAPH: replay a batch whose launches were seen before as one CUDA graph launch
     int extend_octant = 0;           // env CRT_EXTEND_OCTANT: bracket experiment, extend reads a copy of the queue sorted by direction octant (cub radix sort per iteration)
     int blocked = 0;                 // env CRT_WF_BLOCKED: temporal blocking experiment, a part runs its whole batch before the next part starts (one stream)
@@ -283,6 +284,12 @@ struct WarpPool {
 #ifndef CRT_EXTEND_THREADS
 #define CRT_EXTEND_THREADS 256
 #endif
+#ifndef CRT_SHADE_PREFETCH
+#define CRT_SHADE_PREFETCH 1   // 0: k_wf_shade without the L2 prefetches of the next entry's state (experiment)
+#endif
+#ifndef CRT_PRIM_PIPE
+#define CRT_PRIM_PIPE 0   // 1: one primitive record per trip of the test loop, software pipelined (experiment)
+#endif
 #ifndef CRT_PREFETCH_NEXT
 #define CRT_PREFETCH_NEXT 0   // 1: L2 prefetch of the node on top of the traversal stack during every node visit (experiment)
 #endif
@@ -453,6 +460,32 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
         if (!COOP) {   // every lane loops over its own primitives; closest hit kept in registers
             // two records per trip: both loads are in flight before the first test needs its data (leaves of
             // the wall quads hold triangle pairs), which halves the exposed L1/L2 latency of this phase
+#if CRT_PRIM_PIPE
+            // one record per trip, the next record's loads issued before the current one is tested: a warp whose
+            // lanes hold 1, 1, 3 primitives makes 3 trips of one test instead of 2 trips of two
+            if (tg_y) {
+                int i0 = 31 - __clz((int)tg_y);
+                tg_y &= ~(1u << i0);
+                uint32_t cur_idx = tg_x + (uint32_t)i0;
+                PrimLoad cur = load_prim(scene.prims, cur_idx);
+                while (true) {
+                    const bool more = tg_y != 0u;
+                    uint32_t nxt_idx = cur_idx;
+                    PrimLoad nxt = cur;
+                    if (more) {
+                        i0 = 31 - __clz((int)tg_y);
+                        tg_y &= ~(1u << i0);
+                        nxt_idx = tg_x + (uint32_t)i0;
+                        nxt = load_prim(scene.prims, nxt_idx);
+                    }
+                    if (COUNT) c_prims++;
+                    test_prim_loaded(cur, cur_idx, o, d, tmin, rec);
+                    if (!more) break;
+                    cur = nxt;
+                    cur_idx = nxt_idx;
+                }
+            }
+#else
             while (tg_y) {
                 const int i0 = 31 - __clz((int)tg_y);
                 tg_y &= ~(1u << i0);
@@ -465,6 +498,7 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
                 test_prim_loaded(r0, tg_x + (uint32_t)i0, o, d, tmin, rec);
                 if (two) test_prim_loaded(r1, tg_x + (uint32_t)i1, o, d, tmin, rec);
             }
+#endif
         } else {
         // cooperative primitive rounds: pool the warp's (ray, primitive) pairs, one pair per lane
         while (true) {
@@ -621,6 +655,7 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
         if (pix != QUEUE_DEAD) {
             const float4 A = w.A[pix], B = w.B[pix], C = w.C[pix];
             if (C.x == PARKED_T) continue;   // a parked pixel waits for extend to finish its ray: nothing is touched
+#if CRT_SHADE_PREFETCH
             asm volatile("prefetch.global.L2 [%0];" :: "l"(a.fb.accum + pix));   // read only when a path ends, late in the body
             if (pix_next != QUEUE_DEAD) {
                 asm volatile("prefetch.global.L2 [%0];" :: "l"(w.A + pix_next));
@@ -629,6 +664,7 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
 #pragma unroll
                 for (int k = 0; k < 6; k++) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.fb.rng + (size_t)k * n + pix_next));
             }
+#endif
             vec3 o = mk3(A.x, A.y, A.z), d = mk3(B.x, B.y, B.z), thr = mk3(fabsf(A.w), B.w, C.z);   // |A.w|: PARKED_SIGN may be left on it
             const uint32_t book = __float_as_uint(C.w);
             int sample = (int)(book & 0xffffffu), bounce = (int)(book >> 24);
@@ -924,6 +960,7 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&be, k_wf_extend<false, false>, CRT_EXTEND_THREADS, 0);
     if (const char* v = getenv("CRT_SHADE_BULK")) s->shade_bulk = atoi(v);
     if (const char* v = getenv("CRT_WF_GRAPH")) s->use_graph = atoi(v);
+    if (const char* v = getenv("CRT_WF_BATCH")) s->batch = atoi(v) < 1 ? 1 : (atoi(v) > 16 ? 16 : atoi(v));
     if (const char* v = getenv("CRT_WF_BLOCKED")) s->blocked = atoi(v);
     if (const char* v = getenv("CRT_EXTEND_OCTANT")) s->extend_octant = atoi(v);
     if (e == cudaSuccess) e = s->shade_bulk ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bs, k_wf_shade_bulk, 256, 0)
@@ -974,11 +1011,11 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
     WfView w;
     w.A = ws->A; w.B = ws->B; w.C = ws->C;
     const int grid_e = num_sms * ws->blocks_extend, grid_s = num_sms * ws->blocks_shade;
-    const int batch = 16;
+    const int batch = ws->batch;
     const bool timed = times != nullptr && (a.flags & CRT_RENDER_TIME_KERNELS);
     cudaError_t e = cudaSuccess;
     const int parts = ws->parts;
-    const int ev_begin = 3 * batch * CRT_WF_MAX_PARTS;
+    const int ev_begin = 3 * 16 * CRT_WF_MAX_PARTS;
     if (timed && !ws->ev[0])
         for (int i = 0; i < ev_begin + 2 + 4 * CRT_WF_MAX_PARTS && e == cudaSuccess; i++) e = cudaEventCreate(&ws->ev[i]);
     if (e != cudaSuccess) return e;
