@@ -215,9 +215,10 @@ private:
 
 class CUDARenderer {
 public:
-    CUDARenderer(int width, int height, int mode = CRT_MODE_AUTO, int device = 0) : m_Width(width), m_Height(height) {   // CUDARenderer.cuh:31
+    CUDARenderer(int width, int height, int mode = CRT_MODE_AUTO, int device = 0, bool referenceExact = false) : m_Width(width), m_Height(height) {   // CUDARenderer.cuh:31
         crt_config cfg = {};
         cfg.width = width; cfg.height = height; cfg.device = device; cfg.mode = mode;
+        cfg.reference_exact = referenceExact ? 1 : 0;   // ties and unseen triangles as the reference's own BVH decides them (crt_api.h)
         const int rc = crt_create(&m_Ctx, &cfg);
         if (rc != CRT_OK) {
             // crt_create leaves *out_ctx null on failure; its detail message is kept under the null context

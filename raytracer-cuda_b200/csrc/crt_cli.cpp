@@ -18,7 +18,7 @@ namespace {
 
 struct Options {
     std::string scene = "cornell", obj, ppm, pfm, trace;
-    int param = 0, width = 800, height = 600, spp = 0, bounces = 20, frames = 1, gpus = 1, force_nccl = 0, mode = CRT_MODE_AUTO, hq_spp = CRT::HIGH_QUALITY_SAMPLES_PER_PIXEL;
+    int param = 0, width = 800, height = 600, spp = 0, bounces = 20, frames = 1, gpus = 1, force_nccl = 0, ref_exact = 0, mode = CRT_MODE_AUTO, hq_spp = CRT::HIGH_QUALITY_SAMPLES_PER_PIXEL;
     unsigned long long seed = 1804289383ull;
     float orbit = 0.f, vfov = 90.f, aperture = 0.f;   // EntryPoint.cu:11-12 defaults
 };
@@ -27,11 +27,12 @@ void usage() {
     std::printf("usage: crt_cli [--scene cornell|cornell_blob|spheres|terrain] [--param N] [--obj a.obj[,b.obj]]\n"
                 "               [--width W] [--height H] [--spp N] [--bounces B] [--frames F] [--orbit DEG_PER_FRAME]\n"
                 "               [--mode wavefront|megakernel|auto] [--seed S] [--hq-spp N] [--ppm FILE] [--pfm FILE]\n"
-                "               [--controller-trace SCRIPT] [--gpus N] [--nccl]\n"
+                "               [--controller-trace SCRIPT] [--gpus N] [--nccl] [--reference-exact]\n"
                 "  --spp N            one still frame of N samples per pixel (the reference's high-quality frame)\n"
                 "  --frames F         F progressive frames through Raytracer::run (1 spp while the camera moves)\n"
                 "  --gpus N           with --spp: shard the frame's samples over GPUs 0..N-1 of this process (crt_group_*)\n"
                 "  --nccl             with --gpus: reduce with ncclReduce instead of the peer-memory kernel\n"
+                "  --reference-exact  equal-t ties and flat-leaf triangles as the reference's own BVH treats them (slower scene set-up)\n"
                 "  --controller-trace print the camera pose after every scripted frame; host logic only, no GPU\n");
 }
 
@@ -116,7 +117,7 @@ int run(const Options& o) {
                     peer && !o.force_nccl ? "peer-memory kernel" : "ncclReduce", st.render_ms > 0 ? st.rays / (st.render_ms + reduce_ms) / 1e3 : 0.0);
         return 0;
     }
-    CRT::CUDARenderer renderer(o.width, o.height, o.mode);
+    CRT::CUDARenderer renderer(o.width, o.height, o.mode, 0, o.ref_exact != 0);
     CRT::WindowManager window(o.width, o.height);
     renderer.initialize(o.seed);
     renderer.setScene(scene);
@@ -178,6 +179,7 @@ int main(int argc, char** argv) {
         else if (a == "--controller-trace") o.trace = next();
         else if (a == "--gpus") o.gpus = std::atoi(next());
         else if (a == "--nccl") o.force_nccl = 1;
+        else if (a == "--reference-exact") o.ref_exact = 1;
         else if (a == "--mode") { const std::string m = next(); o.mode = m == "wavefront" ? CRT_MODE_WAVEFRONT : m == "megakernel" ? CRT_MODE_MEGAKERNEL : CRT_MODE_AUTO; }
         else { std::fprintf(stderr, "unknown option %s\n", a.c_str()); usage(); return 2; }
     }

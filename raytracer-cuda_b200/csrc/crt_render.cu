@@ -69,8 +69,18 @@ __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
 // Same per-pixel work as CUDAKernels::render, restructured as a single loop with one traversal
 // call site: a lane whose path ended starts its next sample immediately, so every lane of a warp
 // has a ray in flight until its pixel is finished.
+#ifndef CRT_MEGA_SMEM_STACK
+#define CRT_MEGA_SMEM_STACK 4   // entries of the traversal stack in shared memory (0 = all local), as in k_wf_extend
+#endif
 template <bool COUNT>
 __global__ void __launch_bounds__(256) k_render_mega(RenderArgs a) {
+#if CRT_MEGA_SMEM_STACK > 0
+    __shared__ uint2 sstack[CRT_MEGA_SMEM_STACK][256];
+    TravStackShared<CRT_MEGA_SMEM_STACK, 256> st;
+    st.slice = &sstack[0][threadIdx.x];
+#else
+    TravStack st;
+#endif
     int x, y;
     const bool valid = tile_pixel(a.rc.width, a.rc.height, x, y);
     unsigned long long rays = 0, nodes = 0, prims = 0;
@@ -106,7 +116,7 @@ __global__ void __launch_bounds__(256) k_render_mega(RenderArgs a) {
             }
             HitRec h;
             nrays++;
-            if (trace_closest<COUNT>(a.scene, o, d, 0.001f, INFINITY, h, &ctr)) {
+            if (trace_closest_on<COUNT>(st, a.scene, o, d, 0.001f, INFINITY, h, &ctr)) {
                 const Surface s = surface_at(a.scene, h, o, d);
                 if (s.mat < a.scene.num_mats) {
                     const MatRec m = a.scene.mats[s.mat];

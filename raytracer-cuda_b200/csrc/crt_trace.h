@@ -232,9 +232,34 @@ CRT_HD uint32_t next_child(uint32_t& ng_y, uint32_t octinv) {
 #define CRT_POSTPONE_LANES 6
 #endif
 
-struct TravStack {   // kept apart from Traverser so that the scalar state stays in registers
-    uint32_t x[CRT_STACK_ENTRIES], y[CRT_STACK_ENTRIES];
+struct StackEntry {
+    uint32_t x, y;
 };
+struct TravStack {   // kept apart from Traverser so that the scalar state stays in registers; all entries in local memory
+    uint32_t x[CRT_STACK_ENTRIES], y[CRT_STACK_ENTRIES];
+    CRT_HD void set(int k, uint32_t a, uint32_t b) { x[k] = a; y[k] = b; }
+    CRT_HD StackEntry get(int k) const { StackEntry e; e.x = x[k]; e.y = y[k]; return e; }
+};
+#if defined(__CUDACC__)
+// The short stack of the kernels: the first SHARED entries of a thread live in shared memory, laid out
+// [entry][thread] (8-byte accesses of consecutive threads: conflict free), deeper entries spill to local memory.
+// `slice` points at the thread's column of a __shared__ uint2 [SHARED][threads] array.
+template <int SHARED, int THREADS>
+struct TravStackShared {
+    uint2* slice;
+    uint32_t lx[CRT_STACK_ENTRIES - SHARED], ly[CRT_STACK_ENTRIES - SHARED];
+    __device__ __forceinline__ void set(int k, uint32_t a, uint32_t b) {
+        if (k < SHARED) slice[k * THREADS] = make_uint2(a, b);
+        else { lx[k - SHARED] = a; ly[k - SHARED] = b; }
+    }
+    __device__ __forceinline__ StackEntry get(int k) const {
+        StackEntry e;
+        if (k < SHARED) { const uint2 v = slice[k * THREADS]; e.x = v.x; e.y = v.y; }
+        else { e.x = lx[k - SHARED]; e.y = ly[k - SHARED]; }
+        return e;
+    }
+};
+#endif
 
 struct Traverser {
     vec3 o, d;
@@ -261,14 +286,14 @@ struct Traverser {
         ng_x = 0u; ng_y = 0x80000000u;
     }
 
-    template <bool COUNT>
-    CRT_HD bool step(const SceneView& sc, TravStack& st, TraceCounters* ctr, int postpone_lanes = CRT_POSTPONE_LANES) {
+    template <bool COUNT, class Stack>
+    CRT_HD bool step(const SceneView& sc, Stack& st, TraceCounters* ctr, int postpone_lanes = CRT_POSTPONE_LANES) {
         uint32_t tg_x, tg_y;                  // primitive group: (first prim index, hits[23:0])
         if (ng_y & 0xff000000u) {
             const uint32_t base = ng_x;
             uint32_t rest = ng_y;
             const uint32_t rel = next_child(rest, octinv);
-            if (rest & 0xff000000u) { st.x[sp] = base; st.y[sp] = rest; sp++; }
+            if (rest & 0xff000000u) { st.set(sp, base, rest); sp++; }
             if (COUNT) ctr->nodes++;
 #ifdef CRT_NODE_HOOK
             CRT_NODE_HOOK(base + rel);
@@ -285,7 +310,7 @@ struct Traverser {
 #if defined(__CUDA_ARCH__)
             // few lanes hold primitives and this lane still has nodes to visit: keep the group for later
             if ((ng_y & 0xff000000u) && __popc(__activemask()) < postpone_lanes) {
-                st.x[sp] = tg_x; st.y[sp] = tg_y; sp++;
+                st.set(sp, tg_x, tg_y); sp++;
                 break;
             }
 #endif
@@ -309,8 +334,9 @@ struct Traverser {
         if ((ng_y & 0xff000000u) == 0u) {
             if (sp == 0) return true;
             sp--;
-            ng_x = st.x[sp];
-            ng_y = st.y[sp];
+            const StackEntry e = st.get(sp);
+            ng_x = e.x;
+            ng_y = e.y;
         }
         return false;
     }
@@ -326,15 +352,19 @@ CRT_HD void trace_giants(const SceneView& sc, vec3 o, vec3 d, float tmin, HitRec
 }
 
 // Closest hit in [tmin, tmax]. COUNT switches the work counters on (crt_render_counted).
-template <bool COUNT>
-CRT_HD bool trace_closest(const SceneView& sc, vec3 o, vec3 d, float tmin, float tmax, HitRec& rec, TraceCounters* ctr) {
+template <bool COUNT, class Stack>
+CRT_HD bool trace_closest_on(Stack& st, const SceneView& sc, vec3 o, vec3 d, float tmin, float tmax, HitRec& rec, TraceCounters* ctr) {
     Traverser tr;
-    TravStack st;
     tr.begin(o, d, tmin, tmax);
     trace_giants<COUNT>(sc, o, d, tmin, tr.rec, ctr);
     while (!tr.step<COUNT>(sc, st, ctr)) {}
     rec = tr.rec;
     return rec.id >= 0;
+}
+template <bool COUNT>
+CRT_HD bool trace_closest(const SceneView& sc, vec3 o, vec3 d, float tmin, float tmax, HitRec& rec, TraceCounters* ctr) {
+    TravStack st;
+    return trace_closest_on<COUNT>(st, sc, o, d, tmin, tmax, rec, ctr);
 }
 
 }  // namespace crt

@@ -857,6 +857,13 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade_bulk(Ren
 #define CRT_TAIL_THREADS 128
 #endif
 __global__ void __launch_bounds__(CRT_TAIL_THREADS) k_wf_tail(RenderArgs a, WfView w, uint32_t* queue, const uint32_t* qcount, int cur, int lanes, int max_iters, int shade_lanes) {
+#if CRT_SMEM_STACK > 0
+    __shared__ uint2 sstack[CRT_SMEM_STACK][CRT_TAIL_THREADS];
+    TravStackShared<CRT_SMEM_STACK, CRT_TAIL_THREADS> st;
+    st.slice = &sstack[0][threadIdx.x];
+#else
+    TravStack st;
+#endif
     const uint32_t count = qcount[cur];
     const size_t n = (size_t)a.rc.width * a.rc.height;
     const uint32_t lane = threadIdx.x & 31u;
@@ -875,7 +882,6 @@ __global__ void __launch_bounds__(CRT_TAIL_THREADS) k_wf_tail(RenderArgs a, WfVi
         bool touched = false, need_shade = true;
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
         Traverser tr;
-        TravStack st;
         tr.o = mk3(0.f, 0.f, 0.f); tr.d = mk3(0.f, 0.f, 1.f);
         if (alive) {
             const float4 A = w.A[pix], B = w.B[pix], C = w.C[pix];
