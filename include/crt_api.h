@@ -14,7 +14,7 @@
  *    crt_last_error(ctx) returns the message of the last failure on that context.
  *  - host input arrays are copied; the caller keeps ownership.
  *  - device pointers handed out are borrowed, valid until the next crt_set_scene /
- *    crt_resize / crt_destroy on that context.
+ *    crt_destroy on that context.
  *  - one context = one device = one host thread at a time. No global symbols
  *    (the reference's `__constant__ Camera d_camera`, src/Core/Camera.cuh:213, made it
  *    one-renderer-per-process); several contexts may coexist.
