@@ -247,6 +247,18 @@ int crt_render_counted(crt_ctx* ctx, const crt_render_params* params);
 int crt_primary_ids(crt_ctx* ctx, uint64_t seed, uint64_t subsequence_base,
                     int32_t* out_ids, float* out_t);
 
+/* The same buffers as crt_primary_ids (same kernel, bit-identical output) WITHOUT any allocation: the id / t staging
+ * that crt_primary_ids takes from cudaMalloc and frees again lives in a file-scope device array of the library
+ * (CRT_PRIMARY_STATIC_MAX_PIXELS * 8 bytes = 8 MB, held by every GPU that loads the library until the process
+ * exits). For callers that must not reach cudaMalloc / cudaFree: tight serving loops, harnesses that forbid it.
+ * This entry point has NO counterpart in the reference.
+ * width*height above CRT_PRIMARY_STATIC_MAX_PIXELS fails with CRT_E_LIMIT (use crt_primary_ids). All calls on a GPU
+ * share the one array: it keeps the last call's contents (every pixel of the frame is rewritten, nothing needs
+ * clearing), and calls that overlap on the same GPU (two contexts, two host threads) race on it. */
+#define CRT_PRIMARY_STATIC_MAX_PIXELS (1u << 20)
+int crt_primary_ids_static(crt_ctx* ctx, uint64_t seed, uint64_t subsequence_base,
+                           int32_t* out_ids, float* out_t);
+
 /* ---- results -------------------------------------------------------------------- */
 
 /* replaces CUDARenderer::getImageData (reference: src/CUDARenderer.cuh:17) + the D2H

@@ -22,6 +22,7 @@ E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_IO, E_PARSE, E_LIMIT, E_BUSY = -1, -2
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT = 0, 1, 2, 3
 MODE_WAVEFRONT, MODE_MEGAKERNEL, MODE_AUTO = 0, 1, 2
 RENDER_ACCUMULATE, RENDER_NO_TONEMAP, RENDER_TIME_KERNELS, RENDER_ASYNC = 1, 2, 4, 8
+PRIMARY_STATIC_MAX_PIXELS = 1 << 20   # CRT_PRIMARY_STATIC_MAX_PIXELS
 REFERENCE_SEED = 1804289383  # glibc rand() first value = what CUDARenderer::initialize passes (CUDARenderer.cuh:46)
 
 
@@ -98,6 +99,7 @@ def load_library():
         "crt_render_counted": (C.c_int, [P, C.POINTER(RenderParams)]),
         "crt_wait": (C.c_int, [P]),
         "crt_primary_ids": (C.c_int, [P, C.c_uint64, C.c_uint64, P, P]),
+        "crt_primary_ids_static": (C.c_int, [P, C.c_uint64, C.c_uint64, P, P]),
         "crt_get_image_rgba8": (C.c_int, [P, P, C.POINTER(P)]),
         "crt_get_accum": (C.c_int, [P, P, C.POINTER(P)]),
         "crt_set_accum": (C.c_int, [P, P]),
@@ -141,7 +143,7 @@ def load_library():
 
 
 API_FUNCTIONS = ["crt_api_version", "crt_create", "crt_destroy", "crt_last_error", "crt_init_rng", "crt_set_scene",
-                 "crt_set_camera", "crt_render", "crt_render_counted", "crt_wait", "crt_primary_ids", "crt_get_image_rgba8",
+                 "crt_set_camera", "crt_render", "crt_render_counted", "crt_wait", "crt_primary_ids", "crt_primary_ids_static", "crt_get_image_rgba8",
                  "crt_get_accum", "crt_set_accum", "crt_tonemap", "crt_get_rng_state", "crt_set_rng_state",
                  "crt_get_stats", "crt_get_stream", "crt_set_stream", "crt_scene_builtin", "crt_scene_free", "crt_scene_load_obj",
                  "crt_write_ppm", "crt_write_pfm", "crt_checkpoint_save", "crt_checkpoint_load",
@@ -304,6 +306,15 @@ class Renderer:
         ids = np.empty((self.height, self.width), np.int32)
         t = np.empty((self.height, self.width), np.float32)
         self._check(self.lib.crt_primary_ids(self._ctx, int(seed), int(subsequence_base), ids.ctypes.data, t.ctypes.data))
+        return ids, t
+
+    def primary_ids_static(self, seed=REFERENCE_SEED, subsequence_base=0, want_t=True):
+        """crt_primary_ids_static: same buffers, staged in the library's static device array (no cudaMalloc /
+        cudaFree inside the call); CrtError (E_LIMIT) above PRIMARY_STATIC_MAX_PIXELS."""
+        ids = np.empty((self.height, self.width), np.int32)
+        t = np.empty((self.height, self.width), np.float32) if want_t else None
+        self._check(self.lib.crt_primary_ids_static(self._ctx, int(seed), int(subsequence_base), ids.ctypes.data,
+                                                    t.ctypes.data if want_t else None))
         return ids, t
 
     # CUDARenderer::getImageData (+ the D2H copy of WindowManager::drawFrame); row 0 = bottom

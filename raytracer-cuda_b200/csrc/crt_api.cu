@@ -357,6 +357,26 @@ int crt_primary_ids(crt_ctx* ctx, uint64_t seed, uint64_t subsequence_base, int3
     return CRT_OK;
 }
 
+int crt_primary_ids_static(crt_ctx* ctx, uint64_t seed, uint64_t subsequence_base, int32_t* out_ids, float* out_t) {
+    NOT_BUSY(ctx);
+    if (!ctx || !out_ids) return ctx ? fail(ctx, CRT_E_INVALID, "crt_primary_ids_static: null output") : CRT_E_INVALID;
+    if (!ctx->scene_ready || !ctx->cam_ready) return fail(ctx, CRT_E_INVALID, "crt_primary_ids_static: scene and camera must be set");
+    const size_t n = (size_t)ctx->cfg.width * ctx->cfg.height;
+    if (n > (size_t)CRT_PRIMARY_STATIC_MAX_PIXELS)
+        return fail(ctx, CRT_E_LIMIT, "crt_primary_ids_static: " + std::to_string(n) + " pixels exceed the static scratch of " +
+                                          std::to_string((size_t)CRT_PRIMARY_STATIC_MAX_PIXELS) + " pixels (CRT_PRIMARY_STATIC_MAX_PIXELS); use crt_primary_ids");
+    CU(cudaSetDevice(ctx->cfg.device));
+    int32_t* d_ids = nullptr;
+    float* d_t = nullptr;
+    cudaError_t e = launch_primary_static(scene_view(ctx), ctx->cam, ctx->cfg.width, ctx->cfg.height, seed, subsequence_base,
+                                          out_t != nullptr, ctx->cfg.device, ctx->stream, &d_ids, &d_t);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_ids, d_ids, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && out_t) e = cudaMemcpyAsync(out_t, d_t, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) return fail_cuda(ctx, e, "crt_primary_ids_static");
+    return CRT_OK;
+}
+
 int crt_get_image_rgba8(crt_ctx* ctx, void* host, void** out_dev) {
     NOT_BUSY(ctx);
     if (!ctx) return CRT_E_INVALID;

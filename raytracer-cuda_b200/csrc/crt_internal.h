@@ -37,6 +37,10 @@ cudaError_t launch_rng_init(uint32_t* rng_planes, int width, int height, unsigne
 cudaError_t launch_render_mega(const RenderArgs& a, bool counted, int num_sms, cudaStream_t stream, uint32_t* launches);
 cudaError_t launch_primary(const SceneView& scene, const Camera& cam, int width, int height, unsigned long long seed,
                            unsigned long long subseq_base, int32_t* ids, float* t, cudaStream_t stream);
+// Same kernel, ids / t staged in the library's file-scope device array (no allocation); returns where they are.
+cudaError_t launch_primary_static(const SceneView& scene, const Camera& cam, int width, int height, unsigned long long seed,
+                                  unsigned long long subseq_base, bool want_t, int device, cudaStream_t stream,
+                                  int32_t** d_ids, float** d_t);
 cudaError_t launch_tonemap(const FrameBuffers& fb, int width, int height, cudaStream_t stream);
 
 // crt_wavefront.cu

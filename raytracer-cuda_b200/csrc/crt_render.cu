@@ -5,6 +5,10 @@
 #include <cuda_runtime.h>
 #include <curand_kernel.h>
 
+#include <mutex>
+
+#include "../../include/crt_api.h"
+
 #include "crt_internal.h"
 #include "crt_shade.h"
 
@@ -191,6 +195,50 @@ cudaError_t launch_primary(const SceneView& scene, const Camera& cam, int width,
                            unsigned long long subseq_base, int32_t* ids, float* t, cudaStream_t stream) {
     const int tiles = ((width + 15) / 16) * ((height + 15) / 16);
     k_primary<<<tiles, 256, 0, stream>>>(scene, cam, width, height, seed, subseq_base, ids, t);
+    return cudaGetLastError();
+}
+
+// ---- primary-hit ids without any allocation (crt_primary_ids_static) --------------------------
+// The id / t staging buffers that crt_primary_ids takes from cudaMalloc live here in a file-scope device array
+// instead: CRT_PRIMARY_STATIC_MAX_PIXELS * 8 bytes = 8 MB, held by every GPU that loads the library until the
+// process exits. In host code `g_primary_scratch` is only a stand-in for the symbol, not a device address: the
+// address each device maps it at is looked up once per device (that device current) with cudaGetSymbolAddress
+// and handed to the kernel as an ordinary pointer. Every call on a device shares the array: k_primary writes
+// each of the frame's pixels (nothing has to start at zero, stale contents past width*height are never read),
+// and two calls that overlap on the same GPU race on it.
+static __device__ __align__(256) unsigned char g_primary_scratch[(size_t)CRT_PRIMARY_STATIC_MAX_PIXELS * 8];
+
+static constexpr int kMaxStaticDevices = 64;
+static std::mutex g_primary_scratch_mutex;
+static unsigned char* g_primary_scratch_ptr[kMaxStaticDevices] = {};
+
+cudaError_t launch_primary_static(const SceneView& scene, const Camera& cam, int width, int height, unsigned long long seed,
+                                  unsigned long long subseq_base, bool want_t, int device, cudaStream_t stream,
+                                  int32_t** d_ids, float** d_t) {
+    const size_t n = (size_t)width * height;
+    if (device < 0 || device >= kMaxStaticDevices || n == 0 || n > (size_t)CRT_PRIMARY_STATIC_MAX_PIXELS) return cudaErrorInvalidValue;
+    unsigned char* base = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_primary_scratch_mutex);
+        if (!g_primary_scratch_ptr[device]) {
+            int current = -1;
+            cudaError_t e = cudaGetDevice(&current);
+            if (e != cudaSuccess) return e;
+            if (current != device) return cudaErrorInvalidDevice;   // the caller makes the context's device current first
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_primary_scratch);
+            if (e != cudaSuccess) return e;
+            if (!p) return cudaErrorInvalidSymbol;
+            g_primary_scratch_ptr[device] = static_cast<unsigned char*>(p);
+        }
+        base = g_primary_scratch_ptr[device];
+    }
+    int32_t* ids = reinterpret_cast<int32_t*>(base);
+    float* t = want_t ? reinterpret_cast<float*>(base + (size_t)CRT_PRIMARY_STATIC_MAX_PIXELS * 4) : nullptr;
+    const int tiles = ((width + 15) / 16) * ((height + 15) / 16);
+    k_primary<<<tiles, 256, 0, stream>>>(scene, cam, width, height, seed, subseq_base, ids, t);
+    *d_ids = ids;
+    *d_t = t;
     return cudaGetLastError();
 }
 
