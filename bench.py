@@ -228,6 +228,9 @@ def kernel_rooflines(args, kst, st_counted, build, peaks, l2_gbs, traffic_json, 
 
 def main():
     args = parse()
+    # a run that stalls says where: Python stacks of every thread go to stderr every CRT_BENCH_WATCHDOG_S seconds (default 600)
+    import faulthandler
+    faulthandler.dump_traceback_later(float(os.environ.get("CRT_BENCH_WATCHDOG_S", "600")), repeat=True, file=sys.stderr)
     if args.impl == "reference":
         return run_reference(args)
     # stdout carries exactly ONE line (the JSON): everything libraries print there on their own (NCCL's version banner

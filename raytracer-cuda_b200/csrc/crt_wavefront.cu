@@ -296,6 +296,9 @@ struct WarpPool {
 #ifndef CRT_SMEM_STACK
 #define CRT_SMEM_STACK 4   // entries of the traversal stack kept in shared memory (0 = all in local memory); see DESIGN.md 3.2
 #endif
+#ifndef CRT_DEBUG_WATCHDOG
+#define CRT_DEBUG_WATCHDOG 0   // 1 (debug builds only): a warp whose loop passes 2^22 trips prints its lanes' state and leaves
+#endif
 #ifndef CRT_EXTEND_MIN_BLOCKS
 #define CRT_EXTEND_MIN_BLOCKS (1024 / CRT_EXTEND_THREADS)
 #endif
@@ -342,7 +345,17 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
     bool has_ray = false, exhausted = false;
     uint32_t pix = 0;   // | PARKED_LANE while the lane runs a resumed ray
     int drain = drain_rounds;
+#if CRT_DEBUG_WATCHDOG
+    uint32_t wd_trips = 0;
+#endif
     while (true) {
+#if CRT_DEBUG_WATCHDOG
+        if (++wd_trips > (1u << 22)) {
+            printf("WATCHDOG k_wf_extend blk %d thr %d has_ray %d exhausted %d pix %08x sp %d ng %08x %08x rec.t %g o %g %g %g d %g %g %g count %u nres %u cursor %u drain_rounds %d\n",
+                   blockIdx.x, threadIdx.x, (int)has_ray, (int)exhausted, pix, sp, ng_x, ng_y, rec.t, o.x, o.y, o.z, d.x, d.y, d.z, count, nres, qcount[2], drain_rounds);
+            break;
+        }
+#endif
         unsigned idle = __ballot_sync(0xffffffffu, !has_ray);
         if (!exhausted && __popc(idle) >= fetch_lanes) {
             const int n = __popc(idle), leader = __ffs(idle) - 1;
@@ -856,10 +869,17 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade_bulk(Ren
 #ifndef CRT_TAIL_THREADS
 #define CRT_TAIL_THREADS 128
 #endif
+// The tail keeps its whole traversal stack in local memory. With the first entries in shared memory (as in k_wf_extend)
+// the kernel stalled for good on the B200 in the first tail stage of the 3rd or 4th consecutive 2000-spp frame (4 runs of 4;
+// the same source with a trip counter + printf in the loop, or with the local stack, ran 6 frames clean and 1.7 % faster:
+// DESIGN.md 3.4). -DCRT_TAIL_SMEM_STACK=4 rebuilds the stalled variant.
+#ifndef CRT_TAIL_SMEM_STACK
+#define CRT_TAIL_SMEM_STACK 0
+#endif
 __global__ void __launch_bounds__(CRT_TAIL_THREADS) k_wf_tail(RenderArgs a, WfView w, uint32_t* queue, const uint32_t* qcount, int cur, int lanes, int max_iters, int shade_lanes) {
-#if CRT_SMEM_STACK > 0
-    __shared__ uint2 sstack[CRT_SMEM_STACK][CRT_TAIL_THREADS];
-    TravStackShared<CRT_SMEM_STACK, CRT_TAIL_THREADS> st;
+#if CRT_TAIL_SMEM_STACK > 0
+    __shared__ uint2 sstack[CRT_TAIL_SMEM_STACK][CRT_TAIL_THREADS];
+    TravStackShared<CRT_TAIL_SMEM_STACK, CRT_TAIL_THREADS> st;
     st.slice = &sstack[0][threadIdx.x];
 #else
     TravStack st;
@@ -897,7 +917,17 @@ __global__ void __launch_bounds__(CRT_TAIL_THREADS) k_wf_tail(RenderArgs a, WfVi
         // again with its next ray, instead of all lanes waiting for the warp's longest ray before any of them shades.
         // The shade step waits until `shade_lanes` lanes need it (or no lane has a node left to visit), so that its
         // long, branchy body is issued for several lanes at a time (the dynamic-fetch trade of k_wf_extend).
+#if CRT_DEBUG_WATCHDOG
+        uint32_t wd_trips = 0;
+#endif
         while (true) {
+#if CRT_DEBUG_WATCHDOG
+            if (++wd_trips > (1u << 22)) {
+                printf("WATCHDOG k_wf_tail blk %d thr %d alive %d need_shade %d pix %u sample %d bounce %d it %d sp %d ng %08x %08x rec.t %g o %g %g %g d %g %g %g lanes %d count %u\n",
+                       blockIdx.x, threadIdx.x, (int)alive, (int)need_shade, pix, sample, bounce, it, tr.sp, tr.ng_x, tr.ng_y, tr.rec.t, tr.o.x, tr.o.y, tr.o.z, tr.d.x, tr.d.y, tr.d.z, lanes, count);
+                break;
+            }
+#endif
             const unsigned want_shade = __ballot_sync(0xffffffffu, alive && need_shade);
             const unsigned stepping = __ballot_sync(0xffffffffu, alive && !need_shade);
             if ((want_shade | stepping) == 0u) break;
@@ -1063,6 +1093,7 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
     bool first = true;
     // CRT_WF_TRACE=1: one stderr line per batch (iteration, queue lengths, host wall clock) for tuning runs
     const bool trace = getenv("CRT_WF_TRACE") != nullptr;
+    const bool debug_sync = getenv("CRT_WF_DEBUG_SYNC") != nullptr;   // blocking sync + one stderr line after every launch of the tail stages
     const auto trace_t0 = std::chrono::steady_clock::now();
     while (e == cudaSuccess && it < max_iters) {
         int active = 0;
@@ -1134,6 +1165,7 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                         k_wf_extend<false, false><<<grid_e, CRT_EXTEND_THREADS, 0, st>>>(a.scene, w, q.queue[q.cur], q.qcount, q.cur, a.fb.counters, ws->fetch_lanes, 0, q.suspended[par], q.suspended[par ^ 1], par, ws->extend_reverse);
                         q.tail = 2;
                         nl++;
+                        if (debug_sync) { const cudaError_t de = cudaStreamSynchronize(st); fprintf(stderr, "wf_debug it=%lld part %d closing extend done (%s), live %u\n", it, p, cudaGetErrorName(de), q.live); }
                     }
                     // spread the pixels over the warps the machine holds (shared by the parts that are in their tail)
                     int tail_parts = 0;
@@ -1148,6 +1180,7 @@ cudaError_t launch_render_wavefront(WavefrontState* ws, const RenderArgs& a, boo
                     k_wf_tail<<<tail_grid, CRT_TAIL_THREADS, 0, st>>>(a, w, q.queue[q.cur], q.qcount, q.cur, (int)lanes, ws->tail_iters, shade_lanes);
                     if (timed) cudaEventRecord(ws->ev[ev_begin + 3 + 2 * p], st);
                     nl++;
+                    if (debug_sync) { const cudaError_t de = cudaStreamSynchronize(st); fprintf(stderr, "wf_debug it=%lld part %d tail stage done (%s), live %u lanes %d grid %d\n", it, p, cudaGetErrorName(de), q.live, (int)lanes, tail_grid); }
                     continue;
                 }
                 // shade: grid-stride over 148 x occupancy CTAs (CRT_SHADE_PERSISTENT=0: one CTA per 256 queue entries)
