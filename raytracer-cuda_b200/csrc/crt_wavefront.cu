@@ -869,10 +869,10 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade_bulk(Ren
 #ifndef CRT_TAIL_THREADS
 #define CRT_TAIL_THREADS 128
 #endif
-// The tail keeps its whole traversal stack in local memory. With the first entries in shared memory (as in k_wf_extend)
-// the kernel stalled for good on the B200 in the first tail stage of the 3rd or 4th consecutive 2000-spp frame (4 runs of 4;
-// the same source with a trip counter + printf in the loop, or with the local stack, ran 6 frames clean and 1.7 % faster:
-// DESIGN.md 3.4). -DCRT_TAIL_SMEM_STACK=4 rebuilds the stalled variant.
+// The tail keeps its whole traversal stack in local memory: measured 1.7 % faster per frame than the shared-memory form
+// (-DCRT_TAIL_SMEM_STACK=4). That form is also the build in which the loop below stalled on the B200 before its
+// rendezvous got an explicit __syncwarp() (ptxas had compiled the loop-top ballots at the back edge
+// without a divergence check).
 #ifndef CRT_TAIL_SMEM_STACK
 #define CRT_TAIL_SMEM_STACK 0
 #endif
@@ -928,6 +928,7 @@ __global__ void __launch_bounds__(CRT_TAIL_THREADS) k_wf_tail(RenderArgs a, WfVi
                 break;
             }
 #endif
+            __syncwarp();   // the two ballots below are the loop's rendezvous: make the reconvergence explicit (tail stall)
             const unsigned want_shade = __ballot_sync(0xffffffffu, alive && need_shade);
             const unsigned stepping = __ballot_sync(0xffffffffu, alive && !need_shade);
             if ((want_shade | stepping) == 0u) break;
