@@ -21,6 +21,71 @@ __global__ void __launch_bounds__(256) k_for_n(int n, F f) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) f(i);
 }
 
+// All remaining PLOC rounds of at most CRT_PLOC_SMALL clusters in one CTA (crt_bvh_driver.h, PlocSmallArgs): the same
+// functors as the per-round launches, __syncthreads() between the steps (it orders the block's global-memory accesses),
+// and a block-wide exclusive scan (two items per thread) in place of cub::DeviceScan.
+static_assert(CRT_PLOC_SMALL <= 2048, "k_ploc_small scans two items per thread of a 1024-thread CTA");
+__global__ void __launch_bounds__(1024) k_ploc_small(PlocSmallArgs a) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_total;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t* cl_in = a.cl_in;
+    uint32_t* cl_out = a.cl_out;
+    int n = a.n;
+    uint32_t rounds = 0;
+    while (n > 1) {
+        PlocNearestFn fn;
+        fn.blo = a.blo; fn.bhi = a.bhi; fn.cluster = cl_in; fn.nearest = a.nearest; fn.n = n;
+        for (int i = tid; i < n; i += 1024) fn(i);
+        __syncthreads();
+        PlocMergeFn fm;
+        fm.blo = a.blo; fm.bhi = a.bhi; fm.bcount = a.bcount; fm.cluster = cl_in; fm.nearest = a.nearest; fm.merged = a.merged;
+        fm.flags = a.flags; fm.node_counter = a.node_counter;
+        for (int i = tid; i < n; i += 1024) fm(i);
+        __syncthreads();
+        const uint32_t f0 = 2 * tid < n ? a.flags[2 * tid] : 0u, f1 = 2 * tid + 1 < n ? a.flags[2 * tid + 1] : 0u;
+        const uint32_t mine = f0 + f1;
+        uint32_t incl = mine;
+        __syncwarp();   // the loops above leave the lanes of a warp with different trip counts: explicit rendezvous
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += v;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            const uint32_t w = s_warp[lane];
+            uint32_t wi = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, wi, d);
+                if (lane >= d) wi += v;
+            }
+            s_warp[lane] = wi - w;
+            if (lane == 31) s_total = wi;
+        }
+        __syncthreads();
+        const uint32_t excl = s_warp[warp] + incl - mine;
+        if (2 * tid < n) a.pos[2 * tid] = excl;
+        if (2 * tid + 1 < n) a.pos[2 * tid + 1] = excl + f0;
+        const uint32_t total = s_total;
+        __syncthreads();
+        PlocCompactFn fc;
+        fc.merged = a.merged; fc.flags = a.flags; fc.pos = a.pos; fc.cluster_out = cl_out; fc.total = a.total; fc.n = n;
+        for (int i = tid; i < n; i += 1024) fc(i);
+        __syncthreads();
+        if ((int)total >= n || total == 0u) {   // no progress: cannot happen (see PlocNearestFn)
+            if (tid == 0) { a.result[0] = 0xffffffffu; a.result[1] = 0u; }
+            return;
+        }
+        n = (int)total;
+        uint32_t* t = cl_in; cl_in = cl_out; cl_out = t;
+        rounds++;
+    }
+    if (tid == 0) { a.result[0] = rounds; a.result[1] = cl_in[0]; }
+}
+
 struct CudaExec {
     cudaStream_t stream;
     int num_sms;
@@ -80,6 +145,11 @@ struct CudaExec {
         note(cub::DeviceScan::ExclusiveSum(nullptr, bytes, in, out, n, stream));
         ensure_tmp(bytes);
         if (cub_tmp) note(cub::DeviceScan::ExclusiveSum(cub_tmp, bytes, in, out, n, stream));
+    }
+
+    void ploc_small(const PlocSmallArgs& a) {
+        k_ploc_small<<<1, 1024, 0, stream>>>(a);
+        note(cudaGetLastError());
     }
 
     void fill_u32(uint32_t* p, uint32_t v, size_t n) {

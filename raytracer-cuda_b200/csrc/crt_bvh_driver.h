@@ -9,8 +9,12 @@
 //   void fill_u32(uint32_t* p, uint32_t v, size_t n);
 //   void upload(void* dst, const void* src, size_t bytes);    // host -> exec memory
 //   void download(void* dst, const void* src, size_t bytes);  // exec memory -> host (synchronises)
+//   void ploc_small(const PlocSmallArgs& a);                   // all remaining PLOC rounds of <= CRT_PLOC_SMALL clusters
 // The product uses CudaExec (crt_bvh_build.cu); tests/hostsim uses a sequential HostExec.
 #pragma once
+#include <cstdio>
+#include <cstdlib>
+
 #include "crt_bvh_build.h"
 
 namespace crt {
@@ -25,6 +29,58 @@ struct WideBvh {
     uint32_t depth = 0;          // wide levels
     uint32_t ploc_rounds = 0;
 };
+
+// The last rounds of PLOC work on a few hundred clusters each (Cornell + blob: 63 of the 78 rounds have fewer than
+// 2 200), where a round costs its launches and its blocking read-back, not its work. Once the cluster count is at most
+// CRT_PLOC_SMALL the rest of the rounds run in ONE launch of one CTA (k_ploc_small, crt_bvh_build.cu: the same
+// functors, __syncthreads between the steps, a block scan for the compaction).
+#ifndef CRT_PLOC_SMALL
+#define CRT_PLOC_SMALL 2048
+#endif
+struct PlocSmallArgs {
+    f4* blo;
+    f4* bhi;
+    uint32_t* bcount;
+    uint32_t* cl_in;          // n cluster ids, Morton order
+    uint32_t* cl_out;
+    uint32_t* nearest;
+    uint32_t* merged;
+    uint32_t* flags;
+    uint32_t* pos;
+    uint32_t* node_counter;   // binary nodes allocated so far
+    uint32_t* total;          // scratch word of PlocCompactFn
+    uint32_t* result;         // [0] rounds run (0xffffffff: a round made no progress), [1] id of the root cluster
+    int n;
+};
+
+// The rounds of ploc_small as a plain loop over an Exec whose memory the host can read (tests/hostsim's HostExec).
+template <class Exec>
+void ploc_small_on_host(Exec& ex, const PlocSmallArgs& a) {
+    uint32_t* cl_in = a.cl_in;
+    uint32_t* cl_out = a.cl_out;
+    int n = a.n;
+    uint32_t rounds = 0;
+    while (n > 1) {
+        PlocNearestFn fn;
+        fn.blo = a.blo; fn.bhi = a.bhi; fn.cluster = cl_in; fn.nearest = a.nearest; fn.n = n;
+        ex.for_n(n, fn);
+        PlocMergeFn fm;
+        fm.blo = a.blo; fm.bhi = a.bhi; fm.bcount = a.bcount; fm.cluster = cl_in; fm.nearest = a.nearest; fm.merged = a.merged;
+        fm.flags = a.flags; fm.node_counter = a.node_counter;
+        ex.for_n(n, fm);
+        ex.exclusive_scan(a.flags, a.pos, n);
+        PlocCompactFn fc;
+        fc.merged = a.merged; fc.flags = a.flags; fc.pos = a.pos; fc.cluster_out = cl_out; fc.total = a.total; fc.n = n;
+        ex.for_n(n, fc);
+        const uint32_t total = *a.total;
+        if ((int)total >= n || total == 0) { a.result[0] = 0xffffffffu; a.result[1] = 0u; return; }
+        n = (int)total;
+        uint32_t* t = cl_in; cl_in = cl_out; cl_out = t;
+        rounds++;
+    }
+    a.result[0] = rounds;
+    a.result[1] = cl_in[0];
+}
 
 // Temporaries of one build: released on every way out of build_wide_bvh (the early error returns included).
 template <class Exec>
@@ -156,7 +212,25 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
     uint32_t* cl_out = cl_b;
     int n = n0;
     uint32_t rounds = 0;
+    uint32_t root = 0;
+    bool have_root = false;
     while (n > 1) {
+        if (n <= CRT_PLOC_SMALL) {   // the rest of the rounds in one launch
+            uint32_t* result = tmp.template alloc<uint32_t>(2);
+            if (!result) return CRT_E_NOMEM;
+            PlocSmallArgs a;
+            a.blo = blo; a.bhi = bhi; a.bcount = bcount; a.cl_in = cl_in; a.cl_out = cl_out; a.nearest = nearest; a.merged = merged;
+            a.flags = flags; a.pos = pos; a.node_counter = &counters[2]; a.total = &counters[3]; a.result = result; a.n = n;
+            ex.ploc_small(a);
+            uint32_t res[2] = {0xffffffffu, 0u};
+            ex.download(res, result, sizeof(res));
+            if (res[0] == 0xffffffffu) return CRT_E_CUDA;   // no progress: cannot happen (see PlocNearestFn)
+            if (getenv("CRT_BUILD_TRACE_ROUNDS")) fprintf(stderr, "ploc: last %u rounds (from %d clusters) in one launch\n", res[0], n);
+            rounds += res[0];
+            root = res[1];
+            have_root = true;
+            break;
+        }
         PlocNearestFn fn;
         fn.blo = blo; fn.bhi = bhi; fn.cluster = cl_in; fn.nearest = nearest; fn.n = n;
         ex.for_n(n, fn);
@@ -171,12 +245,12 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
         uint32_t total = 0;
         ex.download(&total, &counters[3], sizeof(uint32_t));
         if ((int)total >= n || total == 0) return CRT_E_CUDA;   // no progress: cannot happen (see PlocNearestFn)
+        if (getenv("CRT_BUILD_TRACE_ROUNDS")) fprintf(stderr, "ploc round %u: %d -> %u clusters\n", rounds, n, total);
         n = (int)total;
         uint32_t* t = cl_in; cl_in = cl_out; cl_out = t;
         rounds++;
     }
-    uint32_t root = 0;
-    ex.download(&root, cl_in, sizeof(uint32_t));
+    if (!have_root) ex.download(&root, cl_in, sizeof(uint32_t));
 
     // 4. collapse. Every wide node stands for a distinct binary node (an inner one, or a small subtree that
     // was given its own frame, CollapseFn), of which there are 2N-1; N prim records.

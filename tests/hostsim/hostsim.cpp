@@ -34,6 +34,7 @@ struct HostExec {
     void fill_u32(uint32_t* p, uint32_t v, size_t n) { for (size_t i = 0; i < n; i++) p[i] = v; }
     void upload(void* d, const void* s, size_t b) { memcpy(d, s, b); }
     void download(void* d, const void* s, size_t b) { memcpy(d, s, b); }
+    void ploc_small(const PlocSmallArgs& a) { ploc_small_on_host(*this, a); }
 };
 
 struct hs_scene {

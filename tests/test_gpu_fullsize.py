@@ -135,6 +135,31 @@ def test_c5_progressive_frame_full_size(crt):
     sc.free()
 
 
+@pytest.mark.timeout(180, method="thread")
+def test_consecutive_full_size_frames_finish(crt):
+    """Regression test for the tail stall: in one code generation k_wf_tail never returned from the
+    first tail stage of the 3rd or 4th consecutive headline-size frame. Five 1000-spp frames of BASELINE configs[1]'s
+    scene at 2560x1440 (each frame hands both pixel parts to the tail kernel once, with the other part's extend / shade
+    still running); every frame must finish (pytest-timeout ends the process otherwise), cover every pixel and trace a
+    plausible number of rays."""
+    sc = crt.builtin_scene("cornell_blob", 0)
+    W, H, spp = 2560, 1440, 1000
+    r = _renderer(crt, sc, W, H, crt.MODE_WAVEFRONT)
+    rays = []
+    for frame in range(5):
+        st = r.render(spp, 20)
+        rays.append(int(st.rays))
+        assert st.kernel_launches > 1000
+    acc = r.accum()
+    assert np.all(acc[..., 3] == spp)
+    assert np.isfinite(acc).all()
+    mean = np.mean(rays)
+    assert all(abs(x - mean) < 1e-4 * mean for x in rays), rays      # the frames continue the RNG streams: same count to 0.01 %
+    assert 3.0 < mean / (W * H * spp) < 3.6                            # 3.26 path segments per sample on this scene
+    r.close()
+    sc.free()
+
+
 # ---- equal-t ties -----------------------------------------------------------------------------------------------
 def _tie_scene(crt, same_material):
     """A floor quad, and above it a fan of triangles each present TWICE (same three vertices, so the two copies give
