@@ -31,11 +31,37 @@ struct TraceCounters {
 #define CRT_STACK_ENTRIES 48
 #endif
 
+// L1 eviction priority of the scene loads (experiment): CRT_NODE_L1_HINT 1 = wide nodes evict_last;
+// CRT_PRIM_L1_HINT 1 = primitive records evict_first, 2 = no_allocate. 0 = plain ld.global.nc (__ldg).
+#ifndef CRT_NODE_L1_HINT
+#define CRT_NODE_L1_HINT 0
+#endif
+#ifndef CRT_PRIM_L1_HINT
+#define CRT_PRIM_L1_HINT 0
+#endif
 #if defined(__CUDA_ARCH__)
 CRT_HD int hi_bit(uint32_t v) { return 31 - __clz((int)v); }
 CRT_HD int pop_count(uint32_t v) { return __popc(v); }
-CRT_HD f4 ld_f4(const f4* p) { float4 v = __ldg(reinterpret_cast<const float4*>(p)); f4 r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w; return r; }
-CRT_HD u4 ld_u4(const u4* p) { uint4 v = __ldg(reinterpret_cast<const uint4*>(p)); u4 r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w; return r; }
+CRT_HD f4 ld_f4(const f4* p) {
+    f4 r;
+#if CRT_PRIM_L1_HINT == 1
+    asm("ld.global.nc.L1::evict_first.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+#elif CRT_PRIM_L1_HINT == 2
+    asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+#else
+    float4 v = __ldg(reinterpret_cast<const float4*>(p)); r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w;
+#endif
+    return r;
+}
+CRT_HD u4 ld_u4(const u4* p) {
+    u4 r;
+#if CRT_NODE_L1_HINT == 1
+    asm("ld.global.nc.L1::evict_last.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+#else
+    uint4 v = __ldg(reinterpret_cast<const uint4*>(p)); r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w;
+#endif
+    return r;
+}
 #else
 CRT_HD int hi_bit(uint32_t v) { return 31 - __builtin_clz(v); }
 CRT_HD int pop_count(uint32_t v) { return __builtin_popcount(v); }

@@ -296,6 +296,28 @@ struct WarpPool {
 #ifndef CRT_SMEM_STACK
 #define CRT_SMEM_STACK 4   // entries of the traversal stack kept in shared memory (0 = all in local memory); see DESIGN.md 3.2
 #endif
+// Path state and queue words are touched once per launch: their loads are ld.global.cg (L2 only), so that they do not
+// push nodes and primitive records out of L1 (0: plain loads, 1: extend only, 2: extend and shade; +0.3 % on both scenes,
+// DESIGN.md 3.4)
+#ifndef CRT_STATE_BYPASS_L1
+#define CRT_STATE_BYPASS_L1 2
+#endif
+#if CRT_STATE_BYPASS_L1 >= 1
+#define CRT_LD_STATE_E(p) __ldcg(p)
+#else
+#define CRT_LD_STATE_E(p) (*(p))
+#endif
+#if CRT_STATE_BYPASS_L1 >= 2
+#define CRT_LD_STATE_S(p) __ldcg(p)
+#else
+#define CRT_LD_STATE_S(p) (*(p))
+#endif
+#ifndef CRT_SHADE_PREFETCH_PRIM
+#define CRT_SHADE_PREFETCH_PRIM 0   // 1: shade reads the next entry's hit early and prefetches its primitive record into L1 at the end of the trip (experiment)
+#endif
+#ifndef CRT_STATE_STORE_CG
+#define CRT_STATE_STORE_CG 0        // 1: path-state stores of shade as st.global.cg (experiment)
+#endif
 #ifndef CRT_DEBUG_WATCHDOG
 #define CRT_DEBUG_WATCHDOG 0   // 1 (debug builds only): a warp whose loop passes 2^22 trips prints its lanes' state and leaves
 #endif
@@ -370,13 +392,13 @@ __global__ void __launch_bounds__(CRT_EXTEND_THREADS, CRT_EXTEND_MIN_BLOCKS) k_w
                 // the queue is consumed back to front: shade, which ran just before on this part, swept it front to back,
                 // so the path states it wrote last (still in L2) are the ones read first; the next shade starts at the
                 // front, where this kernel ends
-                pix = i < nres ? (r[0].x | PARKED_LANE) : queue[rev ? count - 1u - i : i - nres];
+                pix = i < nres ? (r[0].x | PARKED_LANE) : CRT_LD_STATE_E(&queue[rev ? count - 1u - i : i - nres]);
                 take = pix != QUEUE_DEAD;
             }
             float4 A = make_float4(0.f, 0.f, 0.f, 0.f), B = A;
             if (take) {
-                A = w.A[pix & PIXEL_MASK];
-                B = w.B[pix & PIXEL_MASK];
+                A = CRT_LD_STATE_E(&w.A[pix & PIXEL_MASK]);
+                B = CRT_LD_STATE_E(&w.B[pix & PIXEL_MASK]);
                 // a parked pixel met in the queue: its ray is in the list, not here
                 take = (pix & PARKED_LANE) || !(__float_as_uint(A.w) & PARKED_SIGN);
             }
@@ -666,7 +688,7 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
         // next trip does not start with a chain of DRAM latencies (queue -> state -> primitive record)
         pix_next = (i + stride < count) ? queue[i + stride] : QUEUE_DEAD;
         if (pix != QUEUE_DEAD) {
-            const float4 A = w.A[pix], B = w.B[pix], C = w.C[pix];
+            const float4 A = CRT_LD_STATE_S(&w.A[pix]), B = CRT_LD_STATE_S(&w.B[pix]), C = CRT_LD_STATE_S(&w.C[pix]);
             if (C.x == PARKED_T) continue;   // a parked pixel waits for extend to finish its ray: nothing is touched
 #if CRT_SHADE_PREFETCH
             asm volatile("prefetch.global.L2 [%0];" :: "l"(a.fb.accum + pix));   // read only when a path ends, late in the body
@@ -678,6 +700,10 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
                 for (int k = 0; k < 6; k++) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.fb.rng + (size_t)k * n + pix_next));
             }
 #endif
+#if CRT_SHADE_PREFETCH_PRIM
+            float2 next_hit = make_float2(-1.f, 0.f);   // (t, record index) of the thread's next entry, written by the extend before this launch
+            if (pix_next != QUEUE_DEAD) next_hit = __ldcg(reinterpret_cast<const float2*>(&w.C[pix_next]));
+#endif
             vec3 o = mk3(A.x, A.y, A.z), d = mk3(B.x, B.y, B.z), thr = mk3(fabsf(A.w), B.w, C.z);   // |A.w|: PARKED_SIGN may be left on it
             const uint32_t book = __float_as_uint(C.w);
             int sample = (int)(book & 0xffffffu), bounce = (int)(book >> 24);
@@ -685,6 +711,13 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
             bool touched = false;
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
             keep = shade_step(a, pix, o, d, thr, sample, bounce, rng, C.x, __float_as_uint(C.y), acc, touched);
+#if CRT_SHADE_PREFETCH_PRIM
+            if (next_hit.x >= 0.f) {
+                const char* rec = reinterpret_cast<const char*>(a.scene.prims + __float_as_uint(next_hit.y));
+                asm volatile("prefetch.global.L1 [%0];" :: "l"(rec));
+                asm volatile("prefetch.global.L1 [%0];" :: "l"(rec + 32));
+            }
+#endif
             if (touched) {
                 if (!keep) {
                     acc.w += (float)a.rc.spp;
@@ -695,10 +728,16 @@ __global__ void __launch_bounds__(256, CRT_SHADE_MIN_BLOCKS) k_wf_shade(RenderAr
             }
             wf_store_rng(a.fb.rng, n, pix, rng);
             if (keep) {
+#if CRT_STATE_STORE_CG
+                __stcg(&w.A[pix], make_float4(o.x, o.y, o.z, thr.x));
+                __stcg(&w.B[pix], make_float4(d.x, d.y, d.z, thr.y));
+                __stcg(reinterpret_cast<float2*>(&w.C[pix]) + 1, make_float2(thr.z, __uint_as_float((uint32_t)sample | ((uint32_t)bounce << 24))));
+#else
                 w.A[pix] = make_float4(o.x, o.y, o.z, thr.x);
                 w.B[pix] = make_float4(d.x, d.y, d.z, thr.y);
                 float2* c2 = reinterpret_cast<float2*>(&w.C[pix]) + 1;
                 *c2 = make_float2(thr.z, __uint_as_float((uint32_t)sample | ((uint32_t)bounce << 24)));
+#endif
             } else {
                 queue[i] = QUEUE_DEAD;   // all samples of this pixel are done
             }
@@ -994,6 +1033,21 @@ cudaError_t wavefront_create(WavefrontState** out, int width, int height) {
     for (int p = 1; p < s->parts && e == cudaSuccess; p++) e = cudaStreamCreateWithFlags(&s->side_stream[p], cudaStreamNonBlocking);
     if (e == cudaSuccess && s->parts > 1) e = cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming);
     int be = 0, bs = 0;
+    // CRT_EXTEND_CARVEOUT / CRT_SHADE_CARVEOUT / CRT_TAIL_CARVEOUT = percent of the SM's shared-memory capacity these kernels ask
+    // the driver to set aside (cudaFuncAttributePreferredSharedMemoryCarveout): the rest of the 256 KB is L1, and extend
+    // lives on its L1 hit rate. Extend needs 4 x 9 KB: 16 % (the 64 KB configuration) instead of the driver's default choice
+    // (100 KB, by the occupancy ncu reports) measured +0.3 %, 100 % measured -2.6 %. -1 = leave the default.
+    {
+        const char* v = getenv("CRT_EXTEND_CARVEOUT");
+        const int pct = v ? atoi(v) : 16;
+        if (pct >= 0) {
+        cudaFuncSetAttribute(k_wf_extend<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        cudaFuncSetAttribute(k_wf_extend<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        cudaFuncSetAttribute(k_wf_extend<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        }
+    }
+    if (const char* v = getenv("CRT_SHADE_CARVEOUT")) cudaFuncSetAttribute(k_wf_shade, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(v));
+    if (const char* v = getenv("CRT_TAIL_CARVEOUT")) cudaFuncSetAttribute(k_wf_tail, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(v));
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&be, k_wf_extend<false, false>, CRT_EXTEND_THREADS, 0);
     if (const char* v = getenv("CRT_SHADE_BULK")) s->shade_bulk = atoi(v);
     if (const char* v = getenv("CRT_WF_GRAPH")) s->use_graph = atoi(v);
