@@ -364,8 +364,12 @@ CRT_HD void GiantRecordsFn::operator()(int k) const { prims[base + (uint32_t)k] 
 // the benchmark scenes: subtrees of 3-5 primitives at the bottom of a PLOC tree each became a node of their own).
 // C_PRIM / C_NODE = 0.7: measured issue cost of a primitive test (60 instructions at ~9 active lanes) against a node
 // visit (250 instructions at ~27 lanes) in k_wf_extend.
+#ifndef CRT_COST_NODE
 #define CRT_COST_NODE 1.0f
+#endif
+#ifndef CRT_COST_PRIM
 #define CRT_COST_PRIM 0.7f
+#endif
 
 struct ParentFn {   // over the inner binary nodes [first_inner, first_inner + n)
     const f4* blo;
