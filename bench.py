@@ -193,6 +193,7 @@ def kernel_rooflines(args, kst, st_counted, build, peaks, l2_gbs, traffic_json, 
             r["ncu_dram_gbs"] = tj.get("dram_bytes_per_launch") / (tj.get("gpu_time_us") * 1e-6) / 1e9 if tj.get("gpu_time_us") else None
             r["ncu_dram_frac_of_hbm"] = (r["ncu_dram_gbs"] / hbm) if r.get("ncu_dram_gbs") else None
             r["ncu_source"] = tj.get("source")
+            r["ncu_counters"] = tj.get("counters")   # L1 / L2 hit rates, pipe utilisation, lanes per instruction, occupancy of that capture
         if extra:
             r.update(extra)
         rows.append(r)
@@ -402,6 +403,13 @@ def main():
                     "kernel_share_of_step": ext["ms"] / k_run["ms"], "hbm_peak_gbs": peaks["hbm_gbs"], "l2_peak_gbs": l2,
                     "frac_of_hbm_copy_peak": ext["achieved_gbs"] / peaks["hbm_gbs"] if ext["achieved_gbs"] else None,
                     "achieved_dram_gbs_ncu": ext.get("ncu_dram_gbs"), "achieved_dram_frac_of_hbm_ncu": ext.get("ncu_dram_frac_of_hbm"),
+                    # the bound that explains the kernel: warp instructions of one launch (committed ncu capture) over this
+                    # run's average launch time, against 148 SMs x 4 schedulers x the SM clock sampled during the timed region
+                    "issue_slots": (lambda c, t_ms, mhz: None if not (c and c.get("warp_instructions") and t_ms and mhz) else {
+                        "warp_instructions_per_launch": c["warp_instructions"], "achieved_ginst_s": c["warp_instructions"] / (t_ms * 1e-3) / 1e9,
+                        "peak_ginst_s": 148 * 4 * mhz * 1e6 / 1e9, "frac": c["warp_instructions"] / (t_ms * 1e-3) / (148 * 4 * mhz * 1e6),
+                        "lanes_per_instruction": c.get("lanes_per_instruction")})(
+                            ext.get("ncu_counters"), ext["ms"] / max(ext["launches"], 1), (clocks or {}).get("sm_mhz")),
                     "kernels": rows,
                     "note": "achieved = algorithmic bytes of k_wf_extend / its summed launch time (CUDA events around every launch, separate pass); "
                             "kernels[] carries the same for every kernel of the frame; see DESIGN.md section 6"}

@@ -74,8 +74,23 @@ def summarise(prefix, names, out_file, header, traffic_file):
                 def val(m):
                     x, un = float(r[h.index(m)].replace(",", "")), u[h.index(m)]
                     return x * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "us": 1, "ms": 1e3, "ns": 1e-3}.get(un, 1)
+                def num(m):
+                    try: return float(r[h.index(m)].replace(",", ""))
+                    except (ValueError, IndexError): return None
                 traffic[KERN.get(name, name)] = {"dram_bytes_per_launch": val("dram__bytes_read.sum") + val("dram__bytes_write.sum"),
                                                  "gpu_time_us": val("gpu__time_duration.sum"),
+                                                 # the counters north_star names, for bench.py's roofline.kernels[].ncu_counters
+                                                 "counters": {"l1_hit_pct": num("l1tex__t_sector_hit_rate.pct"), "l2_hit_pct": num("lts__t_sector_hit_rate.pct"),
+                                                              "l2_throughput_pct_of_peak": num("lts__throughput.avg.pct_of_peak_sustained_elapsed"),
+                                                              "dram_throughput_pct_of_peak": num("dram__throughput.avg.pct_of_peak_sustained_elapsed"),
+                                                              "fma_pipe_pct": num("sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active"),
+                                                              "alu_pipe_pct": num("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
+                                                              "issue_slots_busy_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                                                              "lanes_per_instruction": num("smsp__thread_inst_executed_per_inst_executed.ratio"),
+                                                              "warps_active_pct": num("sm__warps_active.avg.pct_of_peak_sustained_active"),
+                                                              "warp_instructions": num("smsp__inst_executed.sum"),
+                                                              "registers_per_thread": num("launch__registers_per_thread"),
+                                                              "stall_long_scoreboard_per_issue": num("smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio")},
                                                  "source": "profiles/%s (%s, one ncu --set full capture)" % (os.path.basename(out_file), name)}
     if wrote: json.dump(traffic, open(traffic_file, "w"), indent=1)
     else: os.remove(out_file)
