@@ -227,6 +227,16 @@ def kernel_rooflines(args, kst, st_counted, build, peaks, l2_gbs, traffic_json, 
     return ext, rows
 
 
+def issue_slot_roofline(counters, rays, extend_ms, sm_mhz):
+    if not (counters and counters.get("warp_instructions") and rays and extend_ms and sm_mhz):
+        return None
+    per_ray = counters["warp_instructions"] / (2560 * 1440 / 2)
+    ach = per_ray * float(rays) / (extend_ms * 1e-3) / 1e9
+    peak = 148 * 4 * sm_mhz * 1e6 / 1e9
+    return {"warp_instructions_per_ray": per_ray, "achieved_ginst_s": ach, "peak_ginst_s": peak, "frac": ach / peak,
+            "lanes_per_instruction": counters.get("lanes_per_instruction")}
+
+
 def main():
     args = parse()
     # a run that stalls says where: Python stacks of every thread go to stderr every CRT_BENCH_WATCHDOG_S seconds (default 600)
@@ -403,13 +413,10 @@ def main():
                     "kernel_share_of_step": ext["ms"] / k_run["ms"], "hbm_peak_gbs": peaks["hbm_gbs"], "l2_peak_gbs": l2,
                     "frac_of_hbm_copy_peak": ext["achieved_gbs"] / peaks["hbm_gbs"] if ext["achieved_gbs"] else None,
                     "achieved_dram_gbs_ncu": ext.get("ncu_dram_gbs"), "achieved_dram_frac_of_hbm_ncu": ext.get("ncu_dram_frac_of_hbm"),
-                    # the bound that explains the kernel: warp instructions of one launch (committed ncu capture) over this
-                    # run's average launch time, against 148 SMs x 4 schedulers x the SM clock sampled during the timed region
-                    "issue_slots": (lambda c, t_ms, mhz: None if not (c and c.get("warp_instructions") and t_ms and mhz) else {
-                        "warp_instructions_per_launch": c["warp_instructions"], "achieved_ginst_s": c["warp_instructions"] / (t_ms * 1e-3) / 1e9,
-                        "peak_ginst_s": 148 * 4 * mhz * 1e6 / 1e9, "frac": c["warp_instructions"] / (t_ms * 1e-3) / (148 * 4 * mhz * 1e6),
-                        "lanes_per_instruction": c.get("lanes_per_instruction")})(
-                            ext.get("ncu_counters"), ext["ms"] / max(ext["launches"], 1), (clocks or {}).get("sm_mhz")),
+                    # the bound that explains the kernel: warp instructions per ray from the committed ncu capture (one
+                    # steady-state launch = one part = half the pixels of a 2560x1440 frame) x this run's rays / extend time, against
+                    # 148 SMs x 4 schedulers x the SM clock sampled during the timed region
+                    "issue_slots": issue_slot_roofline(ext.get("ncu_counters"), kst.rays, ext["ms"], (clocks or {}).get("sm_mhz")),
                     "kernels": rows,
                     "note": "achieved = algorithmic bytes of k_wf_extend / its summed launch time (CUDA events around every launch, separate pass); "
                             "kernels[] carries the same for every kernel of the frame; see DESIGN.md section 6"}
