@@ -1,7 +1,10 @@
-# Round-end check on one B200 (under gpurun): gpu tests, smoke, reference arm, full bench, ncu captures for profiles/
-set -x
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-python __graft_entry__.py smoke 2>&1 | tail -3
-python bench.py --impl reference --steps 2 --warmup 3 > gpurun_out/r1h_bench_ref.json 2> gpurun_out/r1h_bench_ref.err; tail -c 600 gpurun_out/r1h_bench_ref.json
-python bench.py --steps 2 --warmup 3 > gpurun_out/r1h_bench_n1.json 2> gpurun_out/r1h_bench_n1.err; echo rc=$?; tail -3 gpurun_out/r1h_bench_n1.err; cat gpurun_out/r1h_bench_n1.json
-bash scripts/profile_round.sh r1h > gpurun_out/r1h_profile.log 2>&1; tail -8 gpurun_out/r1h_profile.log
+# Round-end check on one B200 (under gpurun): gpu tests, smoke, reference arm, full bench
+TAG=${1:-r2g}
+mkdir -p gpurun_out
+( timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3 )
+python __graft_entry__.py smoke 2>&1 | tail -2
+timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${TAG}_bench_ref.json 2> gpurun_out/${TAG}_bench_ref.err; cut -c1-260 gpurun_out/${TAG}_bench_ref.json
+CRT_BENCH_WATCHDOG_S=120 timeout 600 python bench.py --steps 3 --warmup 3 > gpurun_out/${TAG}_bench_n1.json 2> gpurun_out/${TAG}_bench_n1.err; echo rc=$?; tail -3 gpurun_out/${TAG}_bench_n1.err; python -c "
+import json; d=json.load(open('gpurun_out/${TAG}_bench_n1.json')); r=d['roofline']
+print(d['value'], d['ms_per_step'], d['e2e']['value'], d['check'], r['frac'], r['issue_slots'], d['clocks'])
+for k in r['kernels']: print(k['kernel'], k.get('ms'), k.get('frac'), (k.get('ncu_counters') or {}).get('l1_hit_pct'))"
