@@ -113,6 +113,36 @@ struct CudaExec {
         free_host_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     }
 
+    // Temporaries of one build come out of ONE arena (bump allocation, 256-byte aligned, released as a whole by
+    // free_arena): a build used to spend more host time inside ~30 cudaMalloc / cudaFree calls (each cudaFree also
+    // drains the device) than the GPU spent on its kernels. A request the arena cannot hold falls back to cudaMalloc.
+    char* arena = nullptr;
+    size_t arena_bytes = 0, arena_used = 0;
+    void reserve_tmp(size_t bytes) {
+        if (arena || getenv("CRT_BUILD_NO_ARENA")) return;
+        arena = alloc<char>(bytes);
+        arena_bytes = arena ? bytes : 0;
+        arena_used = 0;
+    }
+    template <class T> T* alloc_tmp(size_t n) {
+        const size_t bytes = ((n ? n : 1) * sizeof(T) + 255) & ~(size_t)255;
+        if (arena && arena_used + bytes <= arena_bytes) {
+            T* p = reinterpret_cast<T*>(arena + arena_used);
+            arena_used += bytes;
+            return p;
+        }
+        return alloc<T>(n);
+    }
+    void release_tmp(void* p) {
+        if (arena && (char*)p >= arena && (char*)p < arena + arena_bytes) return;
+        release(p);
+    }
+    void free_arena() {
+        if (arena) release(arena);
+        arena = nullptr;
+        arena_bytes = arena_used = 0;
+    }
+
     template <class F> void for_n(int n, const F& f) {
         if (n <= 0) return;
         int blocks = (n + 255) / 256;
@@ -179,6 +209,7 @@ int build_bvh_device(const SceneInput& dev_in, uint32_t leaf_max, cudaStream_t s
     int rc = build_wide_bvh(ex, dev_in, leaf_max, out);
     cudaEventRecord(e1, stream);
     ex.note(cudaStreamSynchronize(stream));
+    ex.free_arena();   // after the stream has drained: nothing of the build still reads it
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, e0, e1) != cudaSuccess) ms = 0.f;
     cudaEventDestroy(e0);

@@ -10,6 +10,9 @@
 //   void upload(void* dst, const void* src, size_t bytes);    // host -> exec memory
 //   void download(void* dst, const void* src, size_t bytes);  // exec memory -> host (synchronises)
 //   void ploc_small(const PlocSmallArgs& a);                   // all remaining PLOC rounds of <= CRT_PLOC_SMALL clusters
+//   void reserve_tmp(size_t bytes);  template<class T> T* alloc_tmp(size_t n);  void release_tmp(void* p);
+//                                                              // temporaries of one build (CudaExec: one arena, so that a
+//                                                              // build costs one cudaMalloc + one cudaFree instead of ~30)
 // The product uses CudaExec (crt_bvh_build.cu); tests/hostsim uses a sequential HostExec.
 #pragma once
 #include <cstdio>
@@ -89,9 +92,9 @@ struct BuildScratch {
     void* ptr[32];
     int n = 0;
     explicit BuildScratch(Exec& e) : ex(e) {}
-    ~BuildScratch() { while (n > 0) ex.release(ptr[--n]); }
+    ~BuildScratch() { while (n > 0) ex.release_tmp(ptr[--n]); }
     template <class T> T* alloc(size_t count) {
-        T* p = n < 32 ? ex.template alloc<T>(count) : nullptr;
+        T* p = n < 32 ? ex.template alloc_tmp<T>(count) : nullptr;
         if (p) ptr[n++] = p;
         return p;
     }
@@ -109,6 +112,9 @@ int build_wide_bvh(Exec& ex, const SceneInput& in, uint32_t leaf_max, WideBvh& o
     if (leaf_max < 1) leaf_max = 1;
     if (leaf_max > 3) leaf_max = 3;
     const uint32_t N_alloc = Nall;
+    // every temporary below, summed: 272 bytes per primitive (boxes 32, Morton keys and values 24, binary nodes 72, cluster
+    // lists and flags 24, collapse tables 104, wide-node map 8, + 8 spare) and 30 allocations' worth of alignment
+    ex.reserve_tmp((size_t)N_alloc * 272 + 30 * 512);
 
     f4* plo = tmp.template alloc<f4>(N_alloc);
     f4* phi = tmp.template alloc<f4>(N_alloc);

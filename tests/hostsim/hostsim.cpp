@@ -35,6 +35,9 @@ struct HostExec {
     void upload(void* d, const void* s, size_t b) { memcpy(d, s, b); }
     void download(void* d, const void* s, size_t b) { memcpy(d, s, b); }
     void ploc_small(const PlocSmallArgs& a) { ploc_small_on_host(*this, a); }
+    void reserve_tmp(size_t) {}
+    template <class T> T* alloc_tmp(size_t n) { return alloc<T>(n); }
+    void release_tmp(void* p) { release(p); }
 };
 
 struct hs_scene {
