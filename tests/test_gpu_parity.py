@@ -99,6 +99,27 @@ def test_wavefront_equals_megakernel_bitwise(crt, W, H, spp, monkeypatch):
     sc.free()
 
 
+@pytest.mark.parametrize("name,param", [("cornell_blob", 0), ("spheres", 0), ("terrain", 300)])
+def test_bvh_build_arena_and_per_allocation_paths_agree(crt, name, param, monkeypatch):
+    """The build takes its temporaries from one arena (CudaExec::reserve_tmp) and runs the PLOC rounds on at most 2048
+    clusters in one launch (k_ploc_small); CRT_BUILD_NO_ARENA=1 is the per-allocation path. Same tree (node count,
+    depth), same primary ids and t bits either way."""
+    sc = crt.builtin_scene(name, param)
+    out = []
+    for no_arena in (False, True):
+        if no_arena:
+            monkeypatch.setenv("CRT_BUILD_NO_ARENA", "1")
+        r = make_renderer(crt, sc, 320, 180, crt.MODE_MEGAKERNEL, aspect=320 / 180)
+        st = r.stats()
+        ids, t = r.primary_ids(SEED, 0)
+        out.append((int(st.bvh_nodes), int(st.bvh_depth), int(st.bvh_prims), ids.copy(), t.copy()))
+        r.close()
+    assert out[0][:3] == out[1][:3]
+    assert np.array_equal(out[0][3], out[1][3]) and np.array_equal(out[0][4].view(np.uint32), out[1][4].view(np.uint32))
+    assert (out[0][3] >= 0).mean() > 0.5
+    sc.free()
+
+
 @pytest.mark.parametrize("env", [{"CRT_WF_GRAPH": "1"}, {"CRT_WF_GRAPH": "1", "CRT_WF_PARTS": "1"},
                                  {"CRT_WF_GRAPH": "1", "CRT_WF_BLOCKED": "1", "CRT_WF_PARTS": "4"}, {"CRT_WF_GRAPH": "0", "CRT_WF_BLOCKED": "1", "CRT_WF_PARTS": "3"}])
 def test_graph_replay_and_blocked_order_bitwise(crt, env, monkeypatch):
