@@ -213,8 +213,9 @@ def kernel_rooflines(args, kst, st_counted, build, peaks, l2_gbs, traffic_json, 
         "every 16 iterations", {"algorithmic_bytes": None})
     row("k_wf_tail", "latency (the frame's serial tail: few pixels, each a chain of dependent path segments)", None, None, kst.tail_ms, None,
         "no byte model: the last <= 150 k pixels per part, one thread per pixel")
-    row("k_rng_init", "alu (cuRAND skip-ahead: 2^67 x subsequence jump per pixel, matrix products in registers)", hbm, npx * 24.0, build.rng_init_ms, 1,
-        "24 B written per pixel; outside the frame (once per crt_init_rng)")
+    row("k_rng_init_coop", "alu + shuffles (block-cooperative XORWOW skip-ahead: one generic 2^67 x subsequence jump per CTA, 255 warp-level "
+        "matrix-vector products for its other pixels)", hbm, npx * 24.0, build.rng_init_ms, 1,
+        "24 B written per pixel; outside the frame (once per crt_init_rng); the first call of a process also pays the module load")
     row("bvh build (k_for_n<...> + cub sort/scan)", "launch latency (one short launch per PLOC step)", None, None, build.bvh_build_ms, None,
         "outside the frame (once per crt_set_scene); %d wide nodes" % int(build.bvh_nodes))
     if world > 1:

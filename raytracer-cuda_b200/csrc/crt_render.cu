@@ -1,10 +1,11 @@
-// crt_render.cu — RNG init, megakernel path tracer, primary-id pass, tonemap (sm_100a).
+// crt_render.cu — RNG init (block-cooperative XORWOW skip-ahead), megakernel path tracer, primary-id pass, tonemap (sm_100a).
 //
 // Replaces CUDAKernels::initRandState and CUDAKernels::render
 // (reference: CudaRayTracer/src/CUDAKernels.h:18-26,147-166).
 #include <cuda_runtime.h>
 #include <curand_kernel.h>
 
+#include <cstdlib>
 #include <mutex>
 
 #include "../../include/crt_api.h"
@@ -43,9 +44,98 @@ __global__ void __launch_bounds__(256) k_rng_init(uint32_t* planes, int width, i
     }
 }
 
+// ---- the same states, computed cooperatively ------------------------------------------------------------------
+// curand_init(seed, n, 0) is v(n) = P(n) v0: v0 depends on the seed only, and P(n) = product over the base-4 digits
+// d_k of n of (A^(4^k))^(d_k), A = the XORWOW step matrix to the power 2^67 (one subsequence). cuRAND ships the
+// 160 x 160 bit matrices A^(4^k) (precalc_xorwow_matrix[k], curand_precalc.h) and curand_init applies them per
+// THREAD: ~16 matrix-vector products of 160 rows each for a 22-bit pixel index, 35 k instructions and a local-memory
+// scratch vector per pixel (8.4 ms for a 2560x1440 frame, ncu: 4.06 G warp instructions, lg-throttle bound).
+// All these matrices are powers of one matrix, so they commute and the 256 consecutive subsequences of a CTA are
+//   v(n0 + r) = A^r v(n0),  r = sum e_k 4^k:   S[r + e 4^k] = A^(4^k) S[r + (e-1) 4^k]   for e = 1..3, k = 0..3
+// i.e. 255 products per CTA after ONE generic v(n0), and each product is done by a WARP: lane l takes row
+// 32 i + l of every state word i (5 rows per lane), then an xor butterfly over the lanes. 127 warp instructions per
+// pixel instead of 1 100. Same bits as curand_init (tests: every pixel of full-size frames against k_rng_init, and
+// the oracle's host restatement). d (the Weyl counter) does not move: a subsequence is a multiple of 2^32 steps.
+__device__ __forceinline__ void xorwow_matvec_warp(const unsigned int* __restrict__ m, const uint32_t (&in)[5], uint32_t (&out)[5], int lane) {
+    uint32_t a0 = 0u, a1 = 0u, a2 = 0u, a3 = 0u, a4 = 0u;
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+        // row i*32 + lane of the matrix: what bit `lane` of state word i contributes (__curand_matvec). Branch-free (the row
+        // is masked, not skipped), so the lanes reach the butterfly below without ever having diverged
+        const uint32_t mask = 0u - ((in[i] >> lane) & 1u);
+        const unsigned int* row = m + 5 * (i * 32 + lane);
+        a0 ^= row[0] & mask; a1 ^= row[1] & mask; a2 ^= row[2] & mask; a3 ^= row[3] & mask; a4 ^= row[4] & mask;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a0 ^= __shfl_xor_sync(0xffffffffu, a0, o);
+        a1 ^= __shfl_xor_sync(0xffffffffu, a1, o);
+        a2 ^= __shfl_xor_sync(0xffffffffu, a2, o);
+        a3 ^= __shfl_xor_sync(0xffffffffu, a3, o);
+        a4 ^= __shfl_xor_sync(0xffffffffu, a4, o);
+    }
+    out[0] = a0; out[1] = a1; out[2] = a2; out[3] = a3; out[4] = a4;
+}
+
+__global__ void __launch_bounds__(256) k_rng_init_coop(uint32_t* planes, unsigned long long n_pixels, unsigned long long seed,
+                                                       unsigned long long base) {
+    __shared__ uint32_t S[256][5];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned long long first = (unsigned long long)blockIdx.x * 256ull;
+    // seed scramble of _curand_init_inplace (curand_kernel.h)
+    const unsigned int s0 = ((unsigned int)seed) ^ 0xaad26b49u;
+    const unsigned int s1 = (unsigned int)(seed >> 32) ^ 0xf7dcefddu;
+    const unsigned int t0 = 1099087573u * s0;
+    const unsigned int t1 = 2591861531u * s1;
+    const uint32_t d0 = 6615241u + t1 + t0;
+    if (warp == 0) {   // v(n0): the generic digit loop of _skipahead_sequence, each product spread over the warp
+        uint32_t v[5] = {123456789u + t0, 362436069u ^ t0, 521288629u + t1, 88675123u ^ t1, 5783321u + t0};
+        unsigned long long p = base + first;
+        int k = 0;
+        while (p) {   // k stays below PRECALC_NUM_MATRICES - 1: the launcher sends larger subsequences to k_rng_init
+            const unsigned int digit = (unsigned int)(p & PRECALC_BLOCK_MASK);
+            for (unsigned int t = 0; t < digit; t++) xorwow_matvec_warp(precalc_xorwow_matrix[k], v, v, lane);
+            p >>= PRECALC_BLOCK_SIZE;
+            k++;
+        }
+        if (lane == 0) { S[0][0] = v[0]; S[0][1] = v[1]; S[0][2] = v[2]; S[0][3] = v[3]; S[0][4] = v[4]; }
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int k = 0; k < 4; k++) {
+        const int span = 1 << (2 * k);   // S[0 .. span) are known
+        for (int e = 1; e <= 3; e++) {
+            for (int r = warp; r < span; r += 8) {
+                const uint32_t* src = S[r + (e - 1) * span];
+                const uint32_t in[5] = {src[0], src[1], src[2], src[3], src[4]};
+                uint32_t out[5];
+                xorwow_matvec_warp(precalc_xorwow_matrix[k], in, out, lane);
+                if (lane == 0) { uint32_t* dst = S[r + e * span]; dst[0] = out[0]; dst[1] = out[1]; dst[2] = out[2]; dst[3] = out[3]; dst[4] = out[4]; }
+            }
+            __syncthreads();
+        }
+    }
+    const unsigned long long pix = first + threadIdx.x;
+    if (pix < n_pixels) {
+        planes[pix] = S[threadIdx.x][0];
+        planes[n_pixels + pix] = S[threadIdx.x][1];
+        planes[2 * n_pixels + pix] = S[threadIdx.x][2];
+        planes[3 * n_pixels + pix] = S[threadIdx.x][3];
+        planes[4 * n_pixels + pix] = S[threadIdx.x][4];
+        planes[5 * n_pixels + pix] = d0;
+    }
+}
+
 cudaError_t launch_rng_init(uint32_t* rng_planes, int width, int height, unsigned long long seed,
                             unsigned long long subseq_base, int num_sms, cudaStream_t stream) {
     const size_t n = (size_t)width * height;
+    // subsequences from 4^31 on leave cuRAND's precalculated matrices (its own routine then squares matrices per thread):
+    // those, and CRT_RNG_INIT_CURAND=1 (the reference path of the tests), go through cuRAND's curand_init
+    const bool in_tables = subseq_base < (1ull << 61) && (unsigned long long)n < (1ull << 61);
+    if (in_tables && !getenv("CRT_RNG_INIT_CURAND")) {
+        k_rng_init_coop<<<(unsigned int)((n + 255) / 256), 256, 0, stream>>>(rng_planes, (unsigned long long)n, seed, subseq_base);
+        return cudaGetLastError();
+    }
     int blocks = (int)((n + 255) / 256);
     const int cap = num_sms * 8;
     if (blocks > cap) blocks = cap;

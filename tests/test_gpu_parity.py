@@ -254,6 +254,26 @@ def test_rng_state_matches_curand_init(crt):
     sc.free()
 
 
+@pytest.mark.parametrize("W,H,seed,base", [(2560, 1440, SEED, 0), (2560, 1440, SEED, 7 * 2560 * 1440), (203, 117, 0x0123456789abcdef, 12345),
+                                          (64, 48, SEED, (1 << 40) + 77), (1, 1, 0, 0)])
+def test_cooperative_rng_init_equals_curand_init(crt, W, H, seed, base, monkeypatch):
+    """crt_init_rng computes the states cooperatively (k_rng_init_coop: one generic skip-ahead per CTA, then 255 matrix-vector
+    products shared by its warps); CRT_RNG_INIT_CURAND=1 runs cuRAND's own curand_init per pixel. Every word of every pixel
+    must agree: a full 2560x1440 frame from base 0 and from rank 7's base, an odd size with a 64-bit seed, a base beyond
+    2^40 (digits 20 and up of the skip-ahead), a single pixel."""
+    r = crt.Renderer(W, H, mode=crt.MODE_MEGAKERNEL)
+    r.initialize(seed, base)
+    coop = r.rng_state().copy()
+    coop_ms = r.stats().rng_init_ms
+    monkeypatch.setenv("CRT_RNG_INIT_CURAND", "1")
+    r.initialize(seed, base)
+    ref = r.rng_state()
+    assert np.array_equal(coop, ref), "%d differing words" % (coop != ref).sum()
+    assert len(np.unique(coop[4])) > min(W * H, 1000) // 2          # the states do differ from pixel to pixel
+    print("rng init %dx%d: cooperative %.3f ms, curand_init %.3f ms" % (W, H, coop_ms, r.stats().rng_init_ms))
+    r.close()
+
+
 @pytest.mark.parametrize("mode", ["mega", "wave"])
 def test_passes_accumulate_like_one_render(crt, mode):
     """spp split into passes (ACCUMULATE) continues the per-pixel streams: same bits as one call,
