@@ -110,6 +110,24 @@ def test_hostsim_is_bit_exact_with_oracle(crt, name, param, res, spp, bounces):
     sc.free()
 
 
+def test_hostsim_ploc_rounds_of_both_kinds(crt):
+    """8 768 triangles: the first PLOC rounds run one by one, the rounds from 2 048 clusters on in the single call of
+    Exec::ploc_small (crt_bvh_driver.h; the product's k_ploc_small). The tree must hold every primitive exactly once and
+    find the oracle's primary hits."""
+    sc = crt.builtin_scene("cornell_blob", 48)
+    assert sc.num_triangles > 4 * 2048
+    hs = HostSim(sc.pointer())
+    check_wide_bvh(hs, sc.num_triangles + sc.num_spheres)
+    osc = ol.OracleScene(sc.pointer())
+    rng = ol.rng_states(SEED, 0, 64, 36)
+    oid, ot = osc.primary(sc.camera, 64, 36, SEED)
+    hid, ht, _, _ = hs.primary(sc.camera, 64, 36, rng)
+    assert np.array_equal(oid, hid) and np.array_equal(ot.view(np.uint32), ht.view(np.uint32))
+    hs.close()
+    osc.close()
+    sc.free()
+
+
 @pytest.mark.parametrize("leaf_max", [1, 2, 3])
 def test_hostsim_leaf_sizes(crt, leaf_max):
     sc = crt.builtin_scene("cornell_blob", 12)
