@@ -163,8 +163,11 @@ __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
 // Same per-pixel work as CUDAKernels::render, restructured as a single loop with one traversal
 // call site: a lane whose path ended starts its next sample immediately, so every lane of a warp
 // has a ray in flight until its pixel is finished.
+// Traversal stack: all in local memory. 4 entries in shared memory (-DCRT_MEGA_SMEM_STACK=4, the layout that pays in
+// k_wf_extend) measured slower on every config here: C3 161.0 vs 156.9 ms, C1 0.752 vs 0.741 ms, C5 2.334 vs 2.229 ms,
+// terrain (16 spp) 124.9 vs 119.3 ms (scripts/r2_call27.sh): the megakernel's warps are register-, not L1-bound.
 #ifndef CRT_MEGA_SMEM_STACK
-#define CRT_MEGA_SMEM_STACK 4   // entries of the traversal stack in shared memory (0 = all local), as in k_wf_extend
+#define CRT_MEGA_SMEM_STACK 0
 #endif
 template <bool COUNT>
 __global__ void __launch_bounds__(256) k_render_mega(RenderArgs a) {
